@@ -1,0 +1,215 @@
+/*
+ * vslam_b200.h -- C ABI of the B200-native ORB front end (libvslam_b200.so).
+ *
+ * This is the drop-in boundary for ONE hot path of p2004dr/visual-slam: ORB
+ * extraction -> brute-force Hamming kNN-2 + Lowe ratio -> RANSAC F/E scoring, pose
+ * recovery and triangulation.  The reference has no FFI of its own: the path is
+ * reached from Python through cv2 calls.  Every entry point below therefore names the
+ * reference call site (file:line under /root/reference) whose cv2 call it replaces;
+ * INTEGRATION.md shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain C, no C++/torch types; all functions return 0 on success or a negative
+ *     vslam_status; vslam_last_error() returns a thread-local message for the last
+ *     failure.  No exceptions, no aborts.
+ *   - pointers named d_* are DEVICE pointers (any allocator: cudaMalloc, torch, ...),
+ *     h_* are HOST pointers, small fixed-size matrices are host pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream).
+ *     Device-pointer entry points only enqueue work; *_host entry points copy in,
+ *     run, copy out and synchronise the stream before returning.
+ *   - there is NO CPU fallback: every entry point needs a CUDA device of compute
+ *     capability 10.x and fails with VSLAM_E_CUDA otherwise.
+ */
+#ifndef VSLAM_B200_H
+#define VSLAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum vslam_status {
+    VSLAM_OK = 0,
+    VSLAM_E_INVALID = -1,   /* bad argument (null pointer, size out of range, ...)        */
+    VSLAM_E_CUDA = -2,      /* CUDA runtime error; text in vslam_last_error()             */
+    VSLAM_E_CAPACITY = -3,  /* an output or tie-staging capacity was exceeded             */
+    VSLAM_E_NOMEM = -4
+} vslam_status;
+
+const char* vslam_last_error(void);
+/* ABI version: major*1000 + minor. */
+int vslam_abi_version(void);
+/* Number of visible CUDA devices (0 when there is no usable driver). */
+int vslam_device_count(void);
+
+/* ------------------------------------------------------------------ extraction */
+
+/* One keypoint as cv2.KeyPoint carries it (extractor.py:65 returns a tuple of these):
+ * pt = (x, y) in level-0 pixels, size = 31*scale, angle in degrees [0,360),
+ * response = Harris score, octave = pyramid level.  class_id is always -1. */
+typedef struct vslam_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave;
+} vslam_keypoint;
+
+/* Parameters of ORBExtractor.__init__ (extractor.py:19-48).  ini_threshold is
+ * stored by the reference and never used, so it has no field here.  Fixed by the
+ * reference's cv2.ORB_create call: edgeThreshold 31, firstLevel 0, WTA_K 2,
+ * HARRIS_SCORE, patchSize 31. */
+typedef struct vslam_orb_params {
+    int32_t width, height;   /* frame size the extractor is planned for                  */
+    int32_t n_features;      /* nfeatures                                                */
+    int32_t n_levels;        /* nlevels (1..16)                                          */
+    int32_t fast_threshold;  /* fastThreshold = min_threshold                            */
+    float scale_factor;      /* scaleFactor                                              */
+    int32_t max_batch;       /* frames per launch the workspace is sized for (>= 1)      */
+    int32_t kp_capacity;     /* keypoint rows per frame in the outputs; 0 = n_features + 64
+                              * (retain-best keeps ties, so a level may exceed its quota) */
+} vslam_orb_params;
+
+typedef struct vslam_orb vslam_orb;
+
+int vslam_orb_create(const vslam_orb_params* params, vslam_orb** out);
+int vslam_orb_destroy(vslam_orb* orb);
+/* Effective keypoint capacity per frame and pyramid geometry of a handle. */
+int vslam_orb_kp_capacity(const vslam_orb* orb);
+int vslam_orb_level_info(const vslam_orb* orb, int level, int* w, int* h, int* pitch,
+                         float* scale, int* quota);
+
+/* Replaces cv2.ORB.detectAndCompute(image, None) at extractor.py:65 for a batch of gray
+ * frames.  d_frames: uint8 [batch][height][pitch].  Outputs (capacity = kp_capacity
+ * rows per frame): d_kp [batch][capacity], d_desc uint8 [batch][capacity][32],
+ * d_count int32 [batch] (true count; rows beyond capacity are dropped but counted).
+ * Order: level-major, ascending (y, x) of the level coordinates inside a level.
+ * cv2 leaves the in-level order unspecified (std::nth_element). */
+int vslam_orb_detect_and_compute(vslam_orb* orb, const uint8_t* d_frames, int batch,
+                                 int pitch, vslam_keypoint* d_kp, uint8_t* d_desc,
+                                 int32_t* d_count, void* stream);
+/* Same call with host buffers (h_frames tightly packed: pitch = width). */
+int vslam_orb_detect_and_compute_host(vslam_orb* orb, const uint8_t* h_frames, int batch,
+                                      vslam_keypoint* h_kp, uint8_t* h_desc,
+                                      int32_t* h_count);
+/* Status of the last extraction on this handle: VSLAM_OK, or VSLAM_E_CAPACITY when
+ * ties at a retain-best cut exceeded the staging capacity (results then differ from
+ * the reference).  Synchronises the stream of that call. */
+int vslam_orb_last_status(vslam_orb* orb);
+
+/* Replaces cv2.ORB.compute(image, keypoints) at extractor.py:83,140: descriptors at
+ * caller-supplied keypoints (level-0 coords, own angle in degrees used as given,
+ * own octave).  Keypoints outside [31, W-31) x [31, H-31) are dropped; survivors are
+ * ordered level-major (stable).  h_desc uint8 [n][32]; h_keep_index int32 [n] receives
+ * the input index of each output row.  *n_out = rows written. */
+int vslam_orb_compute_host(vslam_orb* orb, const uint8_t* h_frame, const float* h_x,
+                           const float* h_y, const float* h_angle, const int32_t* h_octave,
+                           int n, uint8_t* h_desc, int32_t* h_keep_index, int* n_out);
+
+/* Replaces cv2.cvtColor(image, COLOR_BGR2GRAY) at extractor.py:62,81,101. */
+int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_gray);
+
+/* Replaces the 64 cv2.goodFeaturesToTrack(image, n//64, 0.01, 10, mask=cell) calls of
+ * ORBExtractor.distribute_keypoints (extractor.py:115-129): one min-eigenvalue map,
+ * per-cell quality threshold, 3x3 local maxima, greedy min-distance selection.
+ * h_xy float [rows*cols*max_per_cell][2] in the reference's visiting order (cells
+ * row-major, corners in acceptance order); h_cell_count int32 [rows*cols]. */
+int vslam_gftt_grid_host(const uint8_t* h_frame, int height, int width, int rows, int cols,
+                         int max_per_cell, double quality, double min_distance,
+                         float* h_xy, int32_t* h_cell_count, int* n_out);
+
+/* Debug/test taps used by the stage-wise parity tests: copy pyramid level `level`
+ * of frame `frame` of the last batch (raw or blurred) to the host, tightly packed. */
+int vslam_orb_debug_level(vslam_orb* orb, int frame, int level, int blurred, uint8_t* h_out);
+/* Runs only the per-level kernels (pyramid, FAST + NMS, blur) on host frames so that the
+ * candidate lists still hold FAST scores when they are read back. */
+int vslam_orb_debug_run_levels_host(vslam_orb* orb, const uint8_t* h_frames, int batch);
+/* FAST candidates (after NMS and the 31-px border) of one frame/level of the last
+ * batch, unordered: x, y, score.  Returns the count through *n_out. */
+int vslam_orb_debug_candidates(vslam_orb* orb, int frame, int level, int cap, int32_t* h_x,
+                               int32_t* h_y, int32_t* h_score, int* n_out);
+
+/* -------------------------------------------------------------------- matching */
+
+/* Replaces cv2.BFMatcher(NORM_HAMMING).knnMatch(d1, d2, k=2) at matcher.py:70 (and
+ * local_mapper.py:116-117) for a batch of descriptor-set pairs.
+ * d_query  uint8 [pairs][q_stride_rows][32], d_train uint8 [pairs][t_stride_rows][32].
+ * Row counts: nq / nt for every pair, or per pair from the device arrays d_nq / d_nt
+ * when non-NULL (values are clamped to nq / nt, which then act as maxima).
+ * Outputs per query row: d_idx int32 [pairs][nq][2], d_dist int32 [pairs][nq][2];
+ * missing neighbours are (-1, -1).  Ties -> lowest train index (1st and 2nd place). */
+int vslam_bf_knn2_hamming256(const uint8_t* d_query, int nq, long q_stride_rows,
+                             const uint8_t* d_train, int nt, long t_stride_rows,
+                             const int32_t* d_nq, const int32_t* d_nt, int pairs,
+                             int32_t* d_idx, int32_t* d_dist, void* stream);
+int vslam_bf_knn2_hamming256_host(const uint8_t* h_query, int nq, const uint8_t* h_train,
+                                  int nt, int32_t* h_idx, int32_t* h_dist);
+
+/* Replaces the Lowe ratio loop of DescriptorMatcher.match (matcher.py:73-81):
+ * keep row q iff two neighbours exist and (!ratio_test or
+ * (double)(float)d1 < ratio*(double)(float)d2), or exactly one neighbour exists.
+ * Survivors are compacted in ascending query order into d_match int32 [pairs][nq][3]
+ * = (queryIdx, trainIdx, distance) and counted in d_match_count int32 [pairs]. */
+int vslam_ratio_filter(const int32_t* d_idx, const int32_t* d_dist, int nq,
+                       const int32_t* d_nq, int pairs, double ratio, int ratio_test,
+                       int32_t* d_match, int32_t* d_match_count, void* stream);
+
+/* Replaces cv2.BFMatcher.match(d1, d2, mask=mask) at matcher.py:102 (k = 1;
+ * h_mask uint8 [nq][nt] non-zero = allowed, may be NULL). Rows with no allowed
+ * train descriptor get (-1, -1). */
+int vslam_bf_match_masked_host(const uint8_t* h_query, int nq, const uint8_t* h_train, int nt,
+                               const uint8_t* h_mask, int32_t* h_idx, int32_t* h_dist);
+
+/* ------------------------------------------------------------------- front end */
+
+/* The BASELINE.json hot path as one call: extract every frame of the batch, then
+ * match frame i (query) against frame i+1 (train) for i = 0..batch-2 with the ratio
+ * test.  Device buffers; outputs as in the calls above plus d_match
+ * int32 [batch-1][kp_capacity][3] and d_match_count int32 [batch-1].
+ * If d_prev_desc is non-NULL it is the descriptor block (kp_capacity rows, count
+ * *d_prev_count) of the frame preceding frame 0 (the previous batch's or the
+ * neighbouring rank's boundary frame); the outputs then hold `batch` pairs and
+ * pair 0 is (prev, frame 0). */
+int vslam_frontend_run(vslam_orb* orb, const uint8_t* d_frames, int batch, int pitch,
+                       const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
+                       vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count,
+                       int32_t* d_match, int32_t* d_match_count, void* stream);
+int vslam_frontend_run_host(vslam_orb* orb, const uint8_t* h_frames, int batch, double ratio,
+                            vslam_keypoint* h_kp, uint8_t* h_desc, int32_t* h_count,
+                            int32_t* h_match, int32_t* h_match_count);
+
+/* -------------------------------------------------------------------- geometry */
+
+/* Scoring kernel of cv2.findFundamentalMat(FM_RANSAC) (matcher.py:192,
+ * local_mapper.py:136): inlier iff max(d1^2, d2^2) <= thr^2 with the two squared
+ * point-to-epipolar-line distances.  h_F row-major double[9]; points float [n][2]. */
+int vslam_score_fundamental_host(const double* h_F, const float* h_p1, const float* h_p2, int n,
+                                 double thr, uint8_t* h_mask, int* n_inliers);
+/* Scoring kernel of cv2.findEssentialMat(RANSAC) (utils.py:124-125, tracker.py:242):
+ * Sampson error in K-normalised coordinates against (thr / ((fx+fy)/2))^2. */
+int vslam_score_essential_host(const double* h_E, const double* h_K, const float* h_p1,
+                               const float* h_p2, int n, double thr, uint8_t* h_mask,
+                               int* n_inliers);
+/* Replaces cv2.findFundamentalMat(p1, p2, FM_RANSAC, thr, conf) (matcher.py:192):
+ * 7-point hypotheses from a seeded counter-based sampler evaluated in parallel,
+ * winner = the most inliers (lowest hypothesis id on ties) within the adaptive
+ * iteration horizon.  h_F receives the winning minimal solution scaled to F[8] = 1. */
+int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p2, int n, double thr,
+                                  double conf, int max_iters, uint64_t seed, double* h_F,
+                                  uint8_t* h_mask, int* n_inliers);
+/* Replaces cv2.findEssentialMat(p1, p2, K, RANSAC, prob, thr) (utils.py:124-125). */
+int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, const double* h_K,
+                                double prob, double thr, int max_iters, uint64_t seed,
+                                double* h_E, uint8_t* h_mask, int* n_inliers);
+/* Replaces cv2.recoverPose(E, p1, p2, K, mask) (utils.py:133, tracker.py:249).
+ * h_mask_inout uint8 [n] (NULL = all ones on input, no output). */
+int vslam_recover_pose_host(const double* h_E, const float* h_p1, const float* h_p2, int n,
+                            const double* h_K, uint8_t* h_mask_inout, double* h_R, double* h_t,
+                            int* n_good);
+/* Replaces cv2.triangulatePoints(P1, P2, p1.T, p2.T) (utils.py:59): per-point DLT.
+ * h_X float [4][n] (row-major, un-normalised homogeneous, as cv2 returns it). */
+int vslam_triangulate_host(const double* h_P1, const double* h_P2, const float* h_p1,
+                           const float* h_p2, int n, float* h_X);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VSLAM_B200_H */

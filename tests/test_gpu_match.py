@@ -1,0 +1,96 @@
+"""GPU parity of brute-force Hamming kNN-2 + ratio filter (C ABI) against the oracle.
+
+Bar: bit-exact distances and indices given identical descriptors (BASELINE.json).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_desc(n, seed):
+    return np.random.default_rng(seed).integers(0, 256, (n, 32), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (5, 1), (127, 129), (128, 128), (2000, 2000),
+                                   (2049, 777), (300, 5000), (8192, 8192)])
+def test_knn2_random_exact(oracle, nq, nt):
+    from orbslam2 import _native
+    q, t = _rand_desc(nq, nq), _rand_desc(nt, nt + 1)
+    idx, dist = _native.bf_knn2_host(q, t)
+    ridx, rdist = oracle.bf_knn2(q, t)
+    assert np.array_equal(idx, ridx)
+    assert np.array_equal(dist, rdist)
+
+
+def test_knn2_ties_lowest_train_index(oracle):
+    from orbslam2 import _native
+    t = _rand_desc(700, 5)
+    t[[2, 5, 7, 300, 650]] = t[2]          # duplicates: first and second place tie
+    q = np.concatenate([t[2:3], t[650:651], _rand_desc(10, 9)])
+    q[5] = 0
+    t[10] = 0
+    t[400] = 0
+    idx, dist = _native.bf_knn2_host(q, t)
+    ridx, rdist = oracle.bf_knn2(q, t)
+    assert np.array_equal(idx, ridx) and np.array_equal(dist, rdist)
+    assert idx[0].tolist() == [2, 5] and dist[0].tolist() == [0, 0]
+    assert idx[5].tolist() == [10, 400]
+    # low-entropy descriptors: many equal distances
+    q = (_rand_desc(500, 1) & 1) * 255
+    t = (_rand_desc(3000, 2) & 1) * 255
+    idx, dist = _native.bf_knn2_host(q, t)
+    ridx, rdist = oracle.bf_knn2(q, t)
+    assert np.array_equal(idx, ridx) and np.array_equal(dist, rdist)
+
+
+def test_knn2_empty_train_and_masked(oracle):
+    from orbslam2 import _native
+    q = _rand_desc(10, 3)
+    idx, dist = _native.bf_knn2_host(q, np.zeros((0, 32), np.uint8))
+    assert (idx == -1).all() and (dist == -1).all()
+    t = _rand_desc(257, 4)
+    rng = np.random.default_rng(0)
+    mask = (rng.random((10, 257)) < 0.3).astype(np.uint8)
+    mask[3] = 0
+    for m in (None, mask):
+        i1, d1 = _native.bf_match_masked_host(q, t, m)
+        r1, rd1 = oracle.bf_match_masked(q, t, m)
+        assert np.array_equal(i1, r1) and np.array_equal(d1, rd1)
+
+
+def test_ratio_filter_device_matches_oracle(oracle):
+    """Batched device path: knn2 + ratio over several pairs with per-pair live counts."""
+    import torch
+    from orbslam2 import _native
+    L = _native.lib()
+    pairs, cap = 3, 600
+    rng = np.random.default_rng(7)
+    desc = rng.integers(0, 256, (pairs + 1, cap, 32), dtype=np.uint8)
+    # make frame i+1 a noisy copy of frame i so that the ratio test keeps many rows
+    for i in range(1, pairs + 1):
+        flip = (rng.random((cap, 32, 8)) < 0.04)
+        desc[i] = desc[i - 1] ^ np.packbits(flip, axis=2, bitorder="little")[..., 0]
+        desc[i] = desc[i][rng.permutation(cap)]
+    counts = np.array([600, 555, 1, 432], np.int32)
+    d_desc = torch.from_numpy(desc).cuda()
+    d_cnt = torch.from_numpy(counts).cuda()
+    d_idx = torch.empty((pairs, cap, 2), dtype=torch.int32, device="cuda")
+    d_dist = torch.empty_like(d_idx)
+    d_match = torch.empty((pairs, cap, 3), dtype=torch.int32, device="cuda")
+    d_mc = torch.empty(pairs, dtype=torch.int32, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    for ratio in (0.75, 0.8, 0.85):
+        _native.check(L.vslam_bf_knn2_hamming256(d_desc.data_ptr(), cap, cap, d_desc.data_ptr() + cap * 32, cap, cap,
+                                                 d_cnt.data_ptr(), d_cnt.data_ptr() + 4, pairs,
+                                                 d_idx.data_ptr(), d_dist.data_ptr(), C.c_void_p(s)))
+        _native.check(L.vslam_ratio_filter(d_idx.data_ptr(), d_dist.data_ptr(), cap, d_cnt.data_ptr(), pairs,
+                                           ratio, 1, d_match.data_ptr(), d_mc.data_ptr(), C.c_void_p(s)))
+        torch.cuda.synchronize()
+        match, mc = d_match.cpu().numpy(), d_mc.cpu().numpy()
+        for p in range(pairs):
+            ref = oracle.match(desc[p][:counts[p]], desc[p + 1][:counts[p + 1]], ratio)
+            got = [(int(a), int(b), float(c)) for a, b, c in match[p][:mc[p]]]
+            assert got == ref, (p, ratio, len(got), len(ref))

@@ -1,0 +1,193 @@
+// abi_frontend.cu -- matching entry points, the fused front end and the debug taps.
+#include <vector>
+
+#include "common.cuh"
+
+int vs_ensure_host_staging(vslam_orb* o);
+int vs_launch_match_masked(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, const uint8_t* d_mask,
+                           int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
+
+extern "C" int vslam_bf_knn2_hamming256(const uint8_t* d_query, int nq, long q_stride_rows,
+                                        const uint8_t* d_train, int nt, long t_stride_rows,
+                                        const int32_t* d_nq, const int32_t* d_nt, int pairs,
+                                        int32_t* d_idx, int32_t* d_dist, void* stream)
+{
+    VS_REQUIRE(pairs >= 0 && nq >= 0 && nt >= 0, "negative size");
+    if (pairs == 0 || nq == 0) return VSLAM_OK;
+    VS_REQUIRE(d_query && d_idx && d_dist && (d_train || nt == 0), "null argument");
+    VS_REQUIRE(((uintptr_t)d_query & 15) == 0 && ((uintptr_t)d_train & 15) == 0, "descriptors must be 16-byte aligned");
+    return vs_launch_knn2(d_query, nq, q_stride_rows, d_train, nt, t_stride_rows, d_nq, d_nt, pairs,
+                          d_idx, d_dist, (cudaStream_t)stream);
+}
+
+extern "C" int vslam_ratio_filter(const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
+                                  int pairs, double ratio, int ratio_test, int32_t* d_match,
+                                  int32_t* d_match_count, void* stream)
+{
+    VS_REQUIRE(pairs >= 0 && nq >= 0, "negative size");
+    VS_REQUIRE(d_match_count && (nq == 0 || (d_idx && d_dist && d_match)), "null argument");
+    return vs_launch_ratio(d_idx, d_dist, nq, d_nq, pairs, ratio, ratio_test, d_match, d_match_count,
+                           (cudaStream_t)stream);
+}
+
+namespace {
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t n) { VS_CUDA(cudaMalloc(&p, n ? n : 16)); return VSLAM_OK; }
+};
+}
+
+extern "C" int vslam_bf_knn2_hamming256_host(const uint8_t* h_query, int nq, const uint8_t* h_train, int nt,
+                                             int32_t* h_idx, int32_t* h_dist)
+{
+    VS_REQUIRE(nq >= 0 && nt >= 0, "negative size");
+    if (nq == 0) return VSLAM_OK;
+    VS_REQUIRE(h_query && h_idx && h_dist && (h_train || nt == 0), "null argument");
+    DevBuf q, t, i, d;
+    int rc;
+    if ((rc = q.alloc((size_t)nq * 32)) || (rc = t.alloc((size_t)nt * 32)) ||
+        (rc = i.alloc((size_t)nq * 8)) || (rc = d.alloc((size_t)nq * 8)))
+        return rc;
+    VS_CUDA(cudaMemcpy(q.p, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    if (nt) VS_CUDA(cudaMemcpy(t.p, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
+    rc = vs_launch_knn2((const uint8_t*)q.p, nq, nq, (const uint8_t*)t.p, nt, nt, nullptr, nullptr, 1,
+                        (int32_t*)i.p, (int32_t*)d.p, 0);
+    if (rc) return rc;
+    VS_CUDA(cudaMemcpy(h_idx, i.p, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_dist, d.p, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    return VSLAM_OK;
+}
+
+extern "C" int vslam_bf_match_masked_host(const uint8_t* h_query, int nq, const uint8_t* h_train, int nt,
+                                          const uint8_t* h_mask, int32_t* h_idx, int32_t* h_dist)
+{
+    VS_REQUIRE(nq >= 0 && nt >= 0, "negative size");
+    if (nq == 0) return VSLAM_OK;
+    VS_REQUIRE(h_query && h_idx && h_dist && (h_train || nt == 0), "null argument");
+    DevBuf q, t, m, i, d;
+    int rc;
+    if ((rc = q.alloc((size_t)nq * 32)) || (rc = t.alloc((size_t)nt * 32)) ||
+        (rc = i.alloc((size_t)nq * 4)) || (rc = d.alloc((size_t)nq * 4)))
+        return rc;
+    VS_CUDA(cudaMemcpy(q.p, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    if (nt) VS_CUDA(cudaMemcpy(t.p, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
+    if (h_mask) {
+        if ((rc = m.alloc((size_t)nq * nt))) return rc;
+        if (nt) VS_CUDA(cudaMemcpy(m.p, h_mask, (size_t)nq * nt, cudaMemcpyHostToDevice));
+    }
+    rc = vs_launch_match_masked((const uint8_t*)q.p, nq, (const uint8_t*)t.p, nt,
+                                h_mask ? (const uint8_t*)m.p : nullptr, (int32_t*)i.p, (int32_t*)d.p, 0);
+    if (rc) return rc;
+    VS_CUDA(cudaMemcpy(h_idx, i.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_dist, d.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    return VSLAM_OK;
+}
+
+// ---------------------------------------------------------------------------
+extern "C" int vslam_frontend_run(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
+                                  const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
+                                  vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count,
+                                  int32_t* d_match, int32_t* d_match_count, void* stream)
+{
+    VS_REQUIRE(o && d_match && d_match_count, "null argument");
+    VS_REQUIRE(!d_prev_desc || d_prev_count, "d_prev_count required with d_prev_desc");
+    int rc = vslam_orb_detect_and_compute(o, d_frames, batch, pitch, d_kp, d_desc, d_count, stream);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int cap = o->plan.kp_cap;
+    int32_t* m = d_match;
+    int32_t* mc = d_match_count;
+    if (d_prev_desc) {
+        // pair 0 = (previous boundary frame, frame 0)
+        rc = vs_launch_knn2(d_prev_desc, cap, cap, d_desc, cap, cap, d_prev_count, d_count, 1,
+                            o->d_knn_idx, o->d_knn_dist, s);
+        if (rc) return rc;
+        rc = vs_launch_ratio(o->d_knn_idx, o->d_knn_dist, cap, d_prev_count, 1, ratio, 1, m, mc, s);
+        if (rc) return rc;
+        m += (size_t)cap * 3;
+        mc += 1;
+    }
+    if (batch > 1) {
+        // pair i = (frame i, frame i+1): the train block is the query block shifted by one frame
+        rc = vs_launch_knn2(d_desc, cap, cap, d_desc + (size_t)cap * 32, cap, cap, d_count, d_count + 1,
+                            batch - 1, o->d_knn_idx, o->d_knn_dist, s);
+        if (rc) return rc;
+        rc = vs_launch_ratio(o->d_knn_idx, o->d_knn_dist, cap, d_count, batch - 1, ratio, 1, m, mc, s);
+        if (rc) return rc;
+    }
+    return VSLAM_OK;
+}
+
+extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, int batch, double ratio,
+                                       vslam_keypoint* h_kp, uint8_t* h_desc, int32_t* h_count,
+                                       int32_t* h_match, int32_t* h_match_count)
+{
+    VS_REQUIRE(o && h_frames && h_kp && h_desc && h_count && h_match_count, "null argument");
+    VS_REQUIRE(batch >= 1 && batch <= o->prm.max_batch, "batch exceeds max_batch");
+    int rc = vs_ensure_host_staging(o);
+    if (rc) return rc;
+    const VsPlan& p = o->plan;
+    cudaStream_t s = o->stream;
+    const size_t fbytes = (size_t)p.width * p.height;
+    VS_CUDA(cudaMemcpyAsync(o->d_frames, h_frames, batch * fbytes, cudaMemcpyHostToDevice, s));
+    rc = vslam_frontend_run(o, o->d_frames, batch, p.width, nullptr, nullptr, ratio, o->d_kp, o->d_desc,
+                            o->d_count, o->d_match, o->d_match_count, s);
+    if (rc) return rc;
+    VS_CUDA(cudaMemcpyAsync(h_kp, o->d_kp, (size_t)batch * p.kp_cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, s));
+    VS_CUDA(cudaMemcpyAsync(h_desc, o->d_desc, (size_t)batch * p.kp_cap * 32, cudaMemcpyDeviceToHost, s));
+    VS_CUDA(cudaMemcpyAsync(h_count, o->d_count, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    if (batch > 1) {
+        VS_REQUIRE(h_match, "null h_match");
+        VS_CUDA(cudaMemcpyAsync(h_match, o->d_match, (size_t)(batch - 1) * p.kp_cap * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+        VS_CUDA(cudaMemcpyAsync(h_match_count, o->d_match_count, (batch - 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    }
+    VS_CUDA(cudaStreamSynchronize(s));
+    return vslam_orb_last_status(o);
+}
+
+// ---------------------------------------------------------------------------
+extern "C" int vslam_orb_debug_level(vslam_orb* o, int frame, int level, int blurred, uint8_t* h_out)
+{
+    VS_REQUIRE(o && h_out, "null argument");
+    VS_REQUIRE(frame >= 0 && frame < o->last_batch && level >= 0 && level < o->plan.n_levels, "bad frame/level");
+    const VsLevel& L = o->plan.lv[level];
+    VS_CUDA(cudaStreamSynchronize(o->last_stream));
+    const uint8_t* src;
+    size_t pitch;
+    if (level == 0 && !blurred) {
+        src = o->last_frames + (size_t)frame * o->last_pitch * o->plan.height;
+        pitch = o->last_pitch;
+    } else {
+        src = o->d_pyr + (size_t)frame * o->plan.pyr_frame_bytes + (blurred ? L.blur_off : L.raw_off);
+        pitch = L.pitch;
+    }
+    if (L.w == 0) return VSLAM_OK;
+    VS_CUDA(cudaMemcpy2D(h_out, L.w, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost));
+    return VSLAM_OK;
+}
+
+extern "C" int vslam_orb_debug_candidates(vslam_orb* o, int frame, int level, int cap, int32_t* h_x,
+                                          int32_t* h_y, int32_t* h_score, int* n_out)
+{
+    VS_REQUIRE(o && n_out, "null argument");
+    VS_REQUIRE(frame >= 0 && frame < o->last_batch && level >= 0 && level < o->plan.n_levels, "bad frame/level");
+    const VsPlan& p = o->plan;
+    const VsLevel& L = p.lv[level];
+    VS_CUDA(cudaStreamSynchronize(o->last_stream));
+    int32_t n = 0;
+    VS_CUDA(cudaMemcpy(&n, o->d_counters + ((size_t)frame * p.n_levels + level) * VS_CTR_STRIDE + VS_CTR_NCAND,
+                       sizeof(n), cudaMemcpyDeviceToHost));
+    *n_out = n;
+    int m = n < cap ? n : cap;
+    if (m <= 0) return VSLAM_OK;
+    std::vector<VsCand> tmp(m);
+    VS_CUDA(cudaMemcpy(tmp.data(), o->d_cand + (size_t)frame * p.cand_frame_entries + L.cand_off,
+                       (size_t)m * sizeof(VsCand), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < m; ++i) {
+        if (h_x) h_x[i] = tmp[i].x;
+        if (h_y) h_y[i] = tmp[i].y;
+        if (h_score) h_score[i] = (int32_t)tmp[i].v;   // Harris key after a full extraction
+    }
+    return VSLAM_OK;
+}

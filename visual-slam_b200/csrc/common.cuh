@@ -1,0 +1,119 @@
+// common.cuh -- shared declarations of libvslam_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/vslam_b200.h"
+
+#define VS_MAX_LEVELS 16
+#define VS_EDGE 31        // edgeThreshold of cv2.ORB_create, extractor.py:42
+#define VS_HALF_PATCH 15  // patchSize 31, extractor.py:46
+
+// Fused level kernel tile: TW x TH output pixels, halo of 4 (3 for the FAST circle
+// and the 7-tap blur, +1 for the NMS neighbours' scores).
+#define VS_TW 64
+#define VS_TH 32
+#define VS_HALO 4
+
+void vs_set_error(const char* fmt, ...);
+int vs_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define VS_CUDA(call)                                                      \
+    do {                                                                   \
+        cudaError_t e__ = (call);                                          \
+        if (e__ != cudaSuccess) return vs_cuda_fail(e__, #call, __FILE__, __LINE__); \
+    } while (0)
+
+#define VS_REQUIRE(cond, msg)                 \
+    do {                                      \
+        if (!(cond)) {                        \
+            vs_set_error("%s: %s", __func__, msg); \
+            return VSLAM_E_INVALID;           \
+        }                                     \
+    } while (0)
+
+// FAST candidate of one (frame, level): level coordinates + value.  `v` is the FAST
+// score (as float) after the level kernel, then the order-preserving key of the
+// Harris response (0 = dropped at the first retain-best cut) after the Harris kernel.
+struct __align__(8) VsCand {
+    uint16_t x, y;
+    uint32_t v;
+};
+
+struct VsLevel {
+    int w, h, pitch;        // level size and row pitch (bytes) of raw/blur storage
+    float scale;            // (float)pow((double)(float)scale_factor, l)
+    int quota;              // per-level feature quota
+    int cand_cap;           // candidate capacity per frame
+    int stage_cap;          // staging rows per frame for the final per-level selection
+    size_t raw_off, blur_off;   // byte offsets inside one frame's pyramid block
+    size_t cand_off;        // entry offset inside one frame's candidate block
+    size_t stage_off;       // entry offset inside one frame's staging block
+    int tiles_x, tiles_y;
+    int tabx_off, taby_off; // offsets of this level's resize tables (from level l-1) in the table block
+};
+
+// Device-side plan (kernel argument, passed by value through constant bank).
+struct VsPlan {
+    int n_levels, width, height, n_features, fast_thr, kp_cap;
+    VsLevel lv[VS_MAX_LEVELS];
+    size_t pyr_frame_bytes;     // bytes of one frame's pyramid block (raw 1.. + blur 0..)
+    size_t cand_frame_entries;
+    size_t stage_frame_entries;
+};
+
+struct vslam_orb {
+    vslam_orb_params prm;
+    VsPlan plan;
+    int device;
+    // device workspace
+    uint8_t* d_pyr;        // [max_batch][pyr_frame_bytes]
+    VsCand* d_cand;        // [max_batch][cand_frame_entries]
+    VsCand* d_stage;       // [max_batch][stage_frame_entries]  (x, y, response bits)
+    int32_t* d_counters;   // [max_batch][n_levels][VS_CTR_STRIDE]
+    uint32_t* d_tab;       // resize tables: (alpha_q << 16) | i0 per destination column / row
+    int32_t* d_status;     // 1 int: sticky overflow flag
+    // frontend scratch
+    int32_t* d_knn_idx;    // [max_batch][kp_cap][2]
+    int32_t* d_knn_dist;
+    // host staging for *_host entry points
+    uint8_t* d_frames;     // [max_batch][h][pitch0]
+    vslam_keypoint* d_kp;
+    uint8_t* d_desc;
+    int32_t* d_count;
+    int32_t* d_match;
+    int32_t* d_match_count;
+    int frame_pitch;
+    cudaStream_t stream;       // own stream for *_host calls
+    cudaStream_t last_stream;
+    const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)
+    int last_pitch, last_batch;
+};
+
+// counters per (frame, level): [0] candidates, [1] survivors of cut 1, [2] final count,
+// [3] unused, [4..4+256) FAST score histogram
+#define VS_CTR_NCAND 0
+#define VS_CTR_NSURV 1
+#define VS_CTR_NFINAL 2
+#define VS_CTR_HIST 4
+#define VS_CTR_STRIDE (4 + 256)
+
+// kernels / launchers implemented in the other translation units
+int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);
+int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
+                     vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
+int vs_launch_knn2(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
+                   long t_stride, const int32_t* d_nq, const int32_t* d_nt, int pairs,
+                   int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
+int vs_launch_ratio(const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
+                    int pairs, double ratio, int ratio_test, int32_t* d_match,
+                    int32_t* d_match_count, cudaStream_t s);
+
+__host__ __device__ inline int vs_reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = i < 0 ? -i : 2 * n - 2 - i;
+    return i;
+}

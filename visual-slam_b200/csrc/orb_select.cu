@@ -1,0 +1,379 @@
+// orb_select.cu -- keypoint selection, orientation and description.
+//
+//   vs_harris_kernel   first retain-best cut (2*quota by FAST score, ties kept; threshold
+//                      from the 256-bin histogram) + Harris response of the survivors (K3/K4)
+//   vs_select_kernel   second retain-best cut (quota by Harris response, ties kept; exact
+//                      radix select on the order-preserving key), (y, x) sort, staging (K5)
+//   vs_describe_kernel one warp per keypoint: intensity-centroid angle with cv::fastAtan2's
+//                      polynomial (K6), keypoint record, steered rBRIEF on the blurred level (K7b)
+// All of this restates what cv2.ORB.detectAndCompute does behind extractor.py:65.
+#include "common.cuh"
+
+struct VsPat { int8_t x0, y0, x1, y1; };
+__device__ const VsPat g_pattern[256] = {
+#include "rbrief_pattern.inc"
+};
+__device__ __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+__device__ __forceinline__ uint32_t f2key(float f)
+{
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key2f(uint32_t k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// Inclusive suffix sum over 256 values, one per thread (blockDim.x == 256):
+// returns sum_{u >= tid} val[u].  s_w: 8 ints of scratch.
+__device__ __forceinline__ int suffix_sum_256(int val, int* s_w)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int s = val;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_down_sync(0xffffffffu, s, o);
+        if (lane + o < 32) s += t;
+    }
+    __syncthreads();
+    if (lane == 0) s_w[w] = s;
+    __syncthreads();
+    for (int j = w + 1; j < 8; ++j) s += s_w[j];
+    return s;
+}
+
+// Harris response of cv2.ORB (7x7 block of 3x3 Sobel, k = 0.04), SURVEY.md 8(a) K4.
+__device__ __forceinline__ float harris_response(const uint8_t* img, int pitch, int x0, int y0)
+{
+    int a = 0, b = 0, c = 0;
+    int dxm[7], sxm[7], dxc[7], sxc[7];
+    // rows y0-4 .. y0+4; Sobel at row r uses rows r-1, r, r+1
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {
+        const uint8_t* p = img + (size_t)(y0 - 4 + r) * pitch + (x0 - 4);
+        int v[9];
+#pragma unroll
+        for (int j = 0; j < 9; ++j) v[j] = __ldg(p + j);
+        int dxn[7], sxn[7];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+            dxn[j] = v[j + 2] - v[j];
+            sxn[j] = v[j] + 2 * v[j + 1] + v[j + 2];
+        }
+        if (r >= 2) {
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+                int Ix = dxm[j] + 2 * dxc[j] + dxn[j];
+                int Iy = sxn[j] - sxm[j];
+                a += Ix * Ix;
+                b += Iy * Iy;
+                c += Ix * Iy;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 7; ++j) { dxm[j] = dxc[j]; sxm[j] = sxc[j]; dxc[j] = dxn[j]; sxc[j] = sxn[j]; }
+    }
+    const float scale = 1.f / (4 * 7 * 255.f);
+    const float s2 = __fmul_rn(scale, scale);
+    const float s4 = __fmul_rn(__fmul_rn(s2, scale), scale);
+    float fa = (float)a, fb = (float)b, fc = (float)c;
+    float sum = __fadd_rn(fa, fb);
+    float r = __fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc));
+    r = __fsub_rn(r, __fmul_rn(__fmul_rn(0.04f, sum), sum));
+    return __fmul_rn(r, s4);
+}
+
+#define VS_HARRIS_CTAS 4
+
+__global__ void __launch_bounds__(256)
+vs_harris_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frames, int fpitch,
+                 size_t fstride, const uint8_t* __restrict__ pyr, VsCand* __restrict__ cand,
+                 int32_t* __restrict__ counters)
+{
+    __shared__ int s_w[8];
+    __shared__ int s_ge[256];
+    __shared__ int s_thr;
+    const int level = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
+    const VsLevel& L = plan.lv[level];
+    int32_t* ctr = counters + ((size_t)b * plan.n_levels + level) * VS_CTR_STRIDE;
+    const int ncand = ctr[VS_CTR_NCAND];
+    if (ncand == 0) return;
+    const int keep = 2 * L.quota;
+    // first cut: threshold = keep-th largest FAST score, everything >= it survives
+    if (tid == 0) s_thr = keep == 0 ? 256 : 0;
+    __syncthreads();
+    if (ncand > keep && keep > 0) {
+        int ge = suffix_sum_256(ctr[VS_CTR_HIST + tid], s_w);        // #scores >= tid
+        s_ge[tid] = ge;
+        __syncthreads();
+        int ge1 = tid < 255 ? s_ge[tid + 1] : 0;
+        if (ge >= keep && ge1 < keep) s_thr = tid;
+        __syncthreads();
+    }
+    const int thr = s_thr;
+    const uint8_t* img;
+    int pitch;
+    if (level == 0) { img = frames + (size_t)b * fstride; pitch = fpitch; }
+    else { img = pyr + (size_t)b * plan.pyr_frame_bytes + L.raw_off; pitch = L.pitch; }
+    VsCand* cl = cand + (size_t)b * plan.cand_frame_entries + L.cand_off;
+    int nsurv = 0;
+    for (int i = blockIdx.x * 256 + tid; i < ncand; i += VS_HARRIS_CTAS * 256) {
+        VsCand c = cl[i];
+        uint32_t key = 0;
+        if ((int)c.v >= thr) {
+            key = f2key(harris_response(img, pitch, c.x, c.y));
+            if (key == 0) key = 1;
+            ++nsurv;
+        }
+        cl[i].v = key;
+    }
+    // survivor count (warp-aggregated)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nsurv += __shfl_down_sync(0xffffffffu, nsurv, o);
+    if ((tid & 31) == 0 && nsurv) atomicAdd(&ctr[VS_CTR_NSURV], nsurv);
+}
+
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+vs_select_kernel(const __grid_constant__ VsPlan plan, const VsCand* __restrict__ cand,
+                 VsCand* __restrict__ stage, int32_t* __restrict__ counters,
+                 int32_t* __restrict__ status)
+{
+    extern __shared__ unsigned long long s_sort[];
+    __shared__ int s_hist[256];
+    __shared__ int s_w[8];
+    __shared__ int s_digit, s_k, s_cnt;
+    const int level = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const VsLevel& L = plan.lv[level];
+    int32_t* ctr = counters + ((size_t)b * plan.n_levels + level) * VS_CTR_STRIDE;
+    const int ncand = ctr[VS_CTR_NCAND], nsurv = ctr[VS_CTR_NSURV];
+    if (nsurv == 0 || L.quota == 0) return;   // NFINAL stays 0 (counters are zeroed per batch)
+    const VsCand* cl = cand + (size_t)b * plan.cand_frame_entries + L.cand_off;
+
+    uint32_t thr_key = 1;
+    if (nsurv > L.quota) {
+        // exact quota-th largest key by 4 passes of 8-bit radix select
+        uint32_t prefix = 0, mask = 0;
+        if (tid == 0) s_k = L.quota;
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            s_hist[tid] = 0;
+            __syncthreads();
+            for (int i = tid; i < ncand; i += 256) {
+                uint32_t k = cl[i].v;
+                if (k != 0 && (k & mask) == prefix) atomicAdd(&s_hist[(k >> shift) & 255], 1);
+            }
+            __syncthreads();
+            const int k_need = s_k;
+            int ge = suffix_sum_256(s_hist[tid], s_w);
+            int gt = ge - s_hist[tid];
+            if (ge >= k_need && gt < k_need) { s_digit = tid; s_k = k_need - gt; }
+            __syncthreads();
+            prefix |= (uint32_t)s_digit << shift;
+            mask |= 255u << shift;
+        }
+        thr_key = prefix;
+    }
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    const int cap = L.stage_cap;
+    for (int i = tid; i < ncand; i += 256) {
+        VsCand c = cl[i];
+        if (c.v >= thr_key && c.v != 0) {
+            int slot = atomicAdd(&s_cnt, 1);
+            if (slot < cap)
+                s_sort[slot] = ((unsigned long long)(((uint32_t)c.y << 16) | c.x) << 32) | c.v;
+        }
+    }
+    __syncthreads();
+    int n = s_cnt;
+    if (n > cap) {
+        if (tid == 0) atomicExch(status, VSLAM_E_CAPACITY);
+        n = cap;
+    }
+    int np2 = 1;
+    while (np2 < n) np2 <<= 1;
+    for (int i = n + tid; i < np2; i += 256) s_sort[i] = ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < np2; i += 256) {
+                int ixj = i ^ j;
+                if (ixj > i) {
+                    unsigned long long a = s_sort[i], c = s_sort[ixj];
+                    bool up = (i & k) == 0;
+                    if ((a > c) == up) { s_sort[i] = c; s_sort[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    VsCand* st = stage + (size_t)b * plan.stage_frame_entries + L.stage_off;
+    for (int i = tid; i < n; i += 256) {
+        unsigned long long e = s_sort[i];
+        VsCand c;
+        c.x = (uint16_t)((e >> 32) & 0xffff);
+        c.y = (uint16_t)(e >> 48);
+        c.v = __float_as_uint(key2f((uint32_t)e));
+        st[i] = c;
+    }
+    if (tid == 0) ctr[VS_CTR_NFINAL] = n;
+}
+
+// ---------------------------------------------------------------------------
+// cv::fastAtan2 in degrees, float32 without contraction.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x)
+{
+    const float kdeg = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = __fmul_rn(0.9997878412794807f, kdeg), p3 = __fmul_rn(-0.3258083974640975f, kdeg),
+                p5 = __fmul_rn(0.1555786518463281f, kdeg), p7 = __fmul_rn(-0.04432655554792128f, kdeg);
+    const float eps = (float)2.2204460492503131e-16;
+    float ax = fabsf(x), ay = fabsf(y), a, c, c2, t;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        t = __fmul_rn(p7, c2); t = __fadd_rn(t, p5); t = __fmul_rn(t, c2); t = __fadd_rn(t, p3);
+        t = __fmul_rn(t, c2); t = __fadd_rn(t, p1);
+        a = __fmul_rn(t, c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        t = __fmul_rn(p7, c2); t = __fadd_rn(t, p5); t = __fmul_rn(t, c2); t = __fadd_rn(t, p3);
+        t = __fmul_rn(t, c2); t = __fadd_rn(t, p1);
+        a = __fsub_rn(90.f, __fmul_rn(t, c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// IC angle of the radius-15 disc around (x0, y0); all 32 lanes of a warp take part.
+__device__ __forceinline__ float ic_angle_warp(const uint8_t* img, int pitch, int x0, int y0, int lane)
+{
+    const int u = lane - VS_HALF_PATCH;    // lanes 0..30 <-> columns -15..15
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const int au = abs(u);
+        const uint8_t* c = img + (size_t)y0 * pitch + x0 + u;
+        int col = 0, vs = 0;
+#pragma unroll
+        for (int v = -VS_HALF_PATCH; v <= VS_HALF_PATCH; ++v) {
+            if (au <= c_umax[v < 0 ? -v : v]) {
+                int val = __ldg(c + (ptrdiff_t)v * pitch);
+                col += val;
+                vs += v * val;
+            }
+        }
+        m10 = u * col;
+        m01 = vs;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    return fast_atan2_deg((float)m01, (float)m10);
+}
+
+// One 256-bit steered rBRIEF descriptor by one warp: lane j produces byte j.
+// s_pat: pattern transposed so that lane j reads test 8j+t at s_pat[t*32 + j].
+__device__ __forceinline__ uint32_t brief_byte(const uint8_t* blur, const uint8_t* raw, int w, int h,
+                                               int pitch, int raw_pitch, int cx, int cy, float a,
+                                               float b, const uint32_t* s_pat, int lane)
+{
+    uint32_t byte = 0;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        uint32_t pw = s_pat[t * 32 + lane];
+        int val[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            float px = (float)(int8_t)(pw >> (16 * s)), py = (float)(int8_t)(pw >> (16 * s + 8));
+            float fx = __fsub_rn(__fmul_rn(px, a), __fmul_rn(py, b));
+            float fy = __fadd_rn(__fmul_rn(px, b), __fmul_rn(py, a));
+            int ix = cx + __float2int_rn(fx), iy = cy + __float2int_rn(fy);
+            if (ix >= 0 && ix < w && iy >= 0 && iy < h)
+                val[s] = __ldg(blur + (size_t)iy * pitch + ix);
+            else   // OpenCV's bordered pyramid holds REFLECT_101 copies of the unblurred level there
+                val[s] = __ldg(raw + (size_t)vs_reflect101(iy, h) * raw_pitch + vs_reflect101(ix, w));
+        }
+        byte |= (uint32_t)(val[0] < val[1]) << t;
+    }
+    return byte;
+}
+
+__device__ __forceinline__ void load_pattern(uint32_t* s_pat)
+{
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        VsPat p = g_pattern[i];
+        uint32_t w = (uint32_t)(uint8_t)p.x0 | ((uint32_t)(uint8_t)p.y0 << 8) |
+                     ((uint32_t)(uint8_t)p.x1 << 16) | ((uint32_t)(uint8_t)p.y1 << 24);
+        s_pat[(i & 7) * 32 + (i >> 3)] = w;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frames, int fpitch,
+                   size_t fstride, const uint8_t* __restrict__ pyr, const VsCand* __restrict__ stage,
+                   const int32_t* __restrict__ counters, vslam_keypoint* __restrict__ kp_out,
+                   uint8_t* __restrict__ desc_out, int32_t* __restrict__ count_out)
+{
+    __shared__ uint32_t s_pat[256];
+    load_pattern(s_pat);
+    __syncthreads();
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int32_t* ctr = counters + (size_t)b * plan.n_levels * VS_CTR_STRIDE;
+    int level = -1, j = 0, total = 0;
+    for (int l = 0; l < plan.n_levels; ++l) {
+        int n = ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL];
+        if (level < 0 && i < total + n) { level = l; j = i - total; }
+        total += n;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) count_out[b] = total;
+    if (level < 0 || i >= plan.kp_cap) return;
+    const VsLevel& L = plan.lv[level];
+    VsCand c = stage[(size_t)b * plan.stage_frame_entries + L.stage_off + j];
+    const uint8_t* fp = pyr + (size_t)b * plan.pyr_frame_bytes;
+    const uint8_t* raw;
+    int rpitch;
+    if (level == 0) { raw = frames + (size_t)b * fstride; rpitch = fpitch; }
+    else { raw = fp + L.raw_off; rpitch = L.pitch; }
+    const float ang = ic_angle_warp(raw, rpitch, c.x, c.y, lane);
+    const float kx = __fmul_rn((float)c.x, L.scale), ky = __fmul_rn((float)c.y, L.scale);
+    vslam_keypoint* ko = kp_out + (size_t)b * plan.kp_cap + i;
+    if (lane == 0) {
+        ko->x = kx; ko->y = ky; ko->size = __fmul_rn(31.f, L.scale);
+        ko->angle = ang; ko->response = __uint_as_float(c.v); ko->octave = level;
+    }
+    // descriptor centre cvRound(pt * (1/scale)), rotation from the angle in radians
+    const float inv = __fdiv_rn(1.f, L.scale);
+    const int cx = __float2int_rn(__fmul_rn(kx, inv)), cy = __float2int_rn(__fmul_rn(ky, inv));
+    const float rad = __fmul_rn(ang, (float)(3.14159265358979323846 / 180.f));
+    const float ca = (float)cos((double)rad), sa = (float)sin((double)rad);
+    uint32_t byte = brief_byte(fp + L.blur_off, raw, L.w, L.h, L.pitch, rpitch, cx, cy, ca, sa, s_pat, lane);
+    desc_out[((size_t)b * plan.kp_cap + i) * 32 + lane] = (uint8_t)byte;
+}
+
+void vs_configure_select_smem(int bytes)
+{
+    if (bytes > 48 * 1024)
+        cudaFuncSetAttribute(vs_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
+                     vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s)
+{
+    const VsPlan& p = o->plan;
+    const size_t fstride = (size_t)pitch * p.height;
+    vs_harris_kernel<<<dim3(VS_HARRIS_CTAS, p.n_levels, batch), 256, 0, s>>>(
+        p, d_frames, pitch, fstride, o->d_pyr, o->d_cand, o->d_counters);
+    int max_stage = 0;
+    for (int l = 0; l < p.n_levels; ++l) max_stage = max(max_stage, p.lv[l].stage_cap);
+    size_t smem = (size_t)max_stage * sizeof(unsigned long long);
+    vs_select_kernel<<<dim3(p.n_levels, batch), 256, smem, s>>>(p, o->d_cand, o->d_stage,
+                                                               o->d_counters, o->d_status);
+    vs_describe_kernel<<<dim3((p.kp_cap + 7) / 8, batch), 256, 0, s>>>(
+        p, d_frames, pitch, fstride, o->d_pyr, o->d_stage, o->d_counters, d_kp, d_desc, d_count);
+    VS_CUDA(cudaGetLastError());
+    return VSLAM_OK;
+}
