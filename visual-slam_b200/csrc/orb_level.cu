@@ -63,13 +63,21 @@ __device__ __forceinline__ int fast_score(const uint8_t* p, int thr)
         lo3[k] = min(d[k], min(d[(k + 1) & 15], d[(k + 2) & 15]));
         hi3[k] = max(d[k], max(d[(k + 1) & 15], d[(k + 2) & 15]));
     }
-    int best = -256;
+    // NOTE: max(best, max(mn, -mx)) per arc is miscompiled by ptxas 12.9 (and the 580 driver
+    // JIT) for sm_100a: the negation is dropped when the chain is fused into VIMNMX3
+    // (scratch/ft4.cu reproduces it).  Keep the two reductions apart and negate once,
+    // behind an opaque barrier.
+    int best_lo = -256, best_hi = 256;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
         int mn = min(lo3[k], min(lo3[(k + 3) & 15], lo3[(k + 6) & 15]));
         int mx = max(hi3[k], max(hi3[(k + 3) & 15], hi3[(k + 6) & 15]));
-        best = max(best, max(mn, -mx));
+        best_lo = max(best_lo, mn);
+        best_hi = min(best_hi, mx);
     }
+    int neg_hi = -best_hi;
+    asm volatile("" : "+r"(neg_hi));
+    const int best = max(best_lo, neg_hi);
     return best > thr ? best - 1 : 0;
 }
 
