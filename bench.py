@@ -1,0 +1,251 @@
+#!/usr/bin/env python3
+"""bench.py -- frames/sec of the ORB front end (extract + BF-Hamming kNN-2 + ratio).
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W [--impl reference]`,
+launched under torch.distributed.run for N > 1; rank 0 prints ONE JSON line.
+
+Workload (BASELINE.json config 2, "C2"): synthetic 640x480 gray video, 2000 ORB features,
+8 levels, scale 1.2, FAST threshold 7, BF-Hamming kNN-2, Lowe ratio 0.75.  One *step* is one
+pass of the hot path over one batch of B consecutive frames per GPU: extract the B frames,
+match every frame against its predecessor (the predecessor of frame 0 is the previous
+step's last frame, whose descriptors stay on the device) -> B extractions + B matches.
+`value` = frames/sec over all ranks with the frames already resident in HBM;
+`e2e` = the same call through the host-buffer C ABI (pinned host frames in, keypoints,
+descriptors and matches out, copies inside the timed region).
+
+Multi-GPU: frames shard by contiguous range (weak scaling, B*K frames per rank); the only
+exchange is one boundary descriptor block per rank boundary (rank r+1 sends its first
+frame's descriptors to rank r, which matches its last frame against them) over NCCL P2P.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "visual-slam_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    # name: (width, height, n_features, default batch)
+    "c2": (640, 480, 2000, 512),
+    "c3": (1920, 1080, 8000, 64),
+    "c5": (3840, 2160, 16000, 16),
+}
+N_LEVELS, SCALE, FAST_THR, RATIO = 8, 1.2, 7, 0.75
+METRIC = "frames/sec ORB extract+BF-Hamming match, 640x480 2k feats"
+PROF_NAMES = {16: "harris", 17: "select", 18: "describe", 19: "knn2", 20: "ratio"}
+
+
+def level_sizes(w, h):
+    out = []
+    for l in range(N_LEVELS):
+        s = np.float32(np.float64(np.float32(SCALE)) ** l)
+        out.append((int(np.rint(np.float32(w) / s)), int(np.rint(np.float32(h) / s))))
+    return out
+
+
+def level_kernel_bytes(w, h):
+    """Algorithmic HBM bytes of the fused level kernel per frame:
+    sum_{l>=1} (P_{l-1} + P_l) [resize: read parent, write child] + sum P [FAST reads the
+    level] + 2 sum P [blur: read level, write blurred level] -- SURVEY.md 8(d)."""
+    px = [a * b for a, b in level_sizes(w, h)]
+    return sum(px[l - 1] + px[l] for l in range(1, N_LEVELS)) + 3 * sum(px)
+
+
+def extraction_bytes(w, h, n):
+    """B_ext of SURVEY.md 8(d): level kernel bytes + per-keypoint gathers and outputs."""
+    return level_kernel_bytes(w, h) + 2 * n * 81 + n * 749 + n * 512 + n * 56
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------
+# CPU arm: the reference's own path.  The reference is pure Python over OpenCV
+# (extractor.py:38-65, matcher.py:29,70-81); its .py files are not on the GPU box, so the
+# three cv2 calls it makes are issued here verbatim with cv2's own thread pool (kind
+# "reference").  Without cv2 the C oracle port is timed on all cores (kind "port").
+def _cv2_front_end(frames, n_features):
+    import cv2
+    orb = cv2.ORB_create(nfeatures=n_features, scaleFactor=SCALE, nlevels=N_LEVELS, edgeThreshold=31,
+                         firstLevel=0, WTA_K=2, scoreType=cv2.ORB_HARRIS_SCORE, patchSize=31,
+                         fastThreshold=FAST_THR)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)
+    prev, n_match = None, 0
+    for f in frames:
+        _, desc = orb.detectAndCompute(f, None)
+        if prev is not None and desc is not None:
+            for pair in bf.knnMatch(prev, desc, k=2):
+                if len(pair) >= 2:
+                    if pair[0].distance < RATIO * pair[1].distance:
+                        n_match += 1
+                elif len(pair) == 1:
+                    n_match += 1
+        prev = desc
+    return n_match
+
+
+def _oracle_chunk(args):
+    w, h, seed, start, count, n_features = args
+    from oracle import oracle as O
+    from orbslam2.synth import SyntheticVideo
+    v = SyntheticVideo(w, h, seed)
+    prev, n_match = None, 0
+    for k in range(start, start + count):
+        r = O.orb_detect_and_compute(v.frame(k), n_features, SCALE, N_LEVELS, FAST_THR)
+        if prev is not None:
+            n_match += len(O.match(prev, r["desc"], RATIO))
+        prev = r["desc"]
+    return n_match
+
+
+def cpu_front_end_fps(w, h, n_features, frames, budget_s=15.0):
+    """Times the CPU path on a bounded sample of `frames`; returns (fps, cores, kind, sample)."""
+    cores = os.cpu_count() or 1
+    try:
+        import cv2
+        cv2.setNumThreads(cores)
+        _cv2_front_end(frames[:3], n_features)                    # warm-up
+        t0 = time.perf_counter()
+        _cv2_front_end(frames[:4], n_features)
+        per = (time.perf_counter() - t0) / 4
+        n = int(max(8, min(len(frames), budget_s / max(per, 1e-4))))
+        t0 = time.perf_counter()
+        _cv2_front_end(frames[:n], n_features)
+        dt = time.perf_counter() - t0
+        return n / dt, cv2.getNumThreads(), "reference", ("%d frames of the workload through cv2 %s "
+                                                           "detectAndCompute + knnMatch + ratio loop "
+                                                           "(the reference's calls), %d threads"
+                                                           % (n, cv2.__version__, cv2.getNumThreads()))
+    except ImportError:
+        import multiprocessing as mp
+        per_proc = 4
+        with mp.get_context("spawn").Pool(cores) as pool:
+            t0 = time.perf_counter()
+            pool.map(_oracle_chunk, [(w, h, 0, i * per_proc, per_proc, n_features) for i in range(cores)])
+            dt = time.perf_counter() - t0
+        n = cores * per_proc
+        return n / dt, cores, "port", "%d frames through the C oracle port, %d processes" % (n, cores)
+
+
+def run_reference_arm(args, rank):
+    """--impl reference: the reference's CPU path on this box's host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    from orbslam2.synth import SyntheticVideo
+    w, h, nf, _ = WORKLOADS[args.workload]
+    v = SyntheticVideo(w, h, 0)
+    frames = [v.frame(k) for k in range(64)]
+    cores = os.cpu_count() or 1
+    try:
+        import cv2
+        cv2.setNumThreads(cores)
+        kind, threads = "reference", cv2.getNumThreads()
+        run = lambda fr: _cv2_front_end(fr, nf)
+        sample = "cv2 %s calls of extractor.py:38-65 + matcher.py:70-81" % cv2.__version__
+    except ImportError:
+        from oracle import oracle as O
+        kind, threads = "port", 1
+
+        def run(fr):
+            prev = None
+            for f in fr:
+                d = O.orb_detect_and_compute(f, nf, SCALE, N_LEVELS, FAST_THR)["desc"]
+                if prev is not None:
+                    O.match(prev, d, RATIO)
+                prev = d
+        sample = "C oracle port, single thread"
+    per_step = 32 if w <= 640 else 4      # frames per step: a bounded sample of the workload
+    for _ in range(max(args.warmup, 1)):
+        run(frames[:per_step])
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        run(frames[(s % 2) * per_step:(s % 2) * per_step + per_step])
+    dt = time.perf_counter() - t0
+    fps = args.steps * per_step / dt
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(args.workload), "frames_per_step": per_step},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+                             "sample": "%d frames per step; %s" % (per_step, sample)},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(key):
+    w, h, nf, _ = WORKLOADS[key]
+    return ("%s: synthetic %dx%d gray video, %d ORB feats, %d levels, scale %.1f, FAST thr %d, "
+            "BF-Hamming kNN-2 ratio %.2f" % (key.upper(), w, h, nf, N_LEVELS, SCALE, FAST_THR, RATIO))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (0 = workload default)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference_arm(args, rank)
+        return
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        sys.stderr.write("bench.py: --gpus %d needs torch.distributed.run with %d ranks\n" % (args.gpus, args.gpus))
+        sys.exit(2)
+    B = args.batch or WORKLOADS[args.workload][3]
+    sys.modules.setdefault("bench", sys.modules[__name__])
+    from bench_gpu_arm import run_gpu_arm
+    run_gpu_arm(args, rank, world, B)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,223 @@
+"""GPU arm of bench.py (kept in its own file; bench.py is the entry point)."""
+import ctypes as C
+import json
+import os
+import time
+
+import numpy as np
+
+
+def run_gpu_arm(args, rank, world, B):
+    import torch
+    import torch.distributed as dist
+    import bench as BN
+    from orbslam2 import _native
+    from orbslam2.synth import SyntheticVideo
+
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = _native.lib()
+    w, h, nf, _ = BN.WORKLOADS[args.workload]
+    K, W = args.steps, args.warmup
+
+    # ---- synthetic frames: B distinct consecutive frames of this rank's range ----------
+    video = SyntheticVideo(w, h, 0)
+    host_frames = np.empty((B, h, w), np.uint8)
+    canvas_period = 64                      # the synthetic pan repeats every 64 frames
+    uniq = min(B, canvas_period)
+    base = [video.frame(rank * 7 + k) for k in range(uniq)]
+    rng = np.random.default_rng(1234 + rank)
+    for k in range(B):
+        if k < uniq:
+            host_frames[k] = base[k]
+        else:                               # re-noise so that no two frames of a batch are identical
+            f = base[k % uniq].astype(np.int16) + rng.integers(-2, 3, (h, w), dtype=np.int16)
+            host_frames[k] = np.clip(f, 0, 255).astype(np.uint8)
+    frames = torch.from_numpy(host_frames).to(dev)
+
+    orb = _native.OrbHandle(w, h, n_features=nf, scale_factor=BN.SCALE, n_levels=BN.N_LEVELS,
+                            fast_threshold=BN.FAST_THR, max_batch=B)
+    cap = orb.kp_capacity
+    kp = torch.empty((B, cap, 6), dtype=torch.float32, device=dev)
+    desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    count = torch.zeros(B, dtype=torch.int32, device=dev)
+    match = torch.empty((B, cap, 3), dtype=torch.int32, device=dev)
+    mcount = torch.zeros(B, dtype=torch.int32, device=dev)
+    prev_desc = torch.zeros((cap, 32), dtype=torch.uint8, device=dev)
+    prev_count = torch.zeros(1, dtype=torch.int32, device=dev)
+    nb_desc = torch.zeros((cap, 32), dtype=torch.uint8, device=dev)      # neighbour's first frame
+    nb_count = torch.zeros(1, dtype=torch.int32, device=dev)
+    first_desc = torch.zeros((cap, 32), dtype=torch.uint8, device=dev)
+    first_count = torch.zeros(1, dtype=torch.int32, device=dev)
+    b_idx = torch.empty((cap, 2), dtype=torch.int32, device=dev)
+    b_dist = torch.empty((cap, 2), dtype=torch.int32, device=dev)
+    b_match = torch.empty((cap, 3), dtype=torch.int32, device=dev)
+    b_mcount = torch.zeros(1, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream()
+    sptr = C.c_void_p(stream.cuda_stream)
+
+    def step(first):
+        _native.check(L.vslam_frontend_run(orb.handle, frames.data_ptr(), B, w,
+                                           None if first else prev_desc.data_ptr(),
+                                           None if first else prev_count.data_ptr(), BN.RATIO,
+                                           kp.data_ptr(), desc.data_ptr(), count.data_ptr(),
+                                           match.data_ptr(), mcount.data_ptr(), sptr))
+        prev_desc.copy_(desc[B - 1], non_blocking=True)
+        prev_count.copy_(count[B - 1:B], non_blocking=True)
+
+    def boundary_exchange():
+        """rank r+1 -> rank r: descriptors of its first frame (one block per rank boundary)."""
+        if world == 1:
+            return []
+        first_desc.copy_(desc[0])
+        first_count.copy_(count[0:1])
+        ops = []
+        if rank > 0:
+            ops += [dist.P2POp(dist.isend, first_desc, rank - 1), dist.P2POp(dist.isend, first_count, rank - 1)]
+        if rank < world - 1:
+            ops += [dist.P2POp(dist.irecv, nb_desc, rank + 1), dist.P2POp(dist.irecv, nb_count, rank + 1)]
+        return dist.batch_isend_irecv(ops) if ops else []
+
+    def boundary_match():
+        if world == 1 or rank == world - 1:
+            return
+        _native.check(L.vslam_bf_knn2_hamming256(prev_desc.data_ptr(), cap, cap, nb_desc.data_ptr(), cap, cap,
+                                                 prev_count.data_ptr(), nb_count.data_ptr(), 1,
+                                                 b_idx.data_ptr(), b_dist.data_ptr(), sptr))
+        _native.check(L.vslam_ratio_filter(b_idx.data_ptr(), b_dist.data_ptr(), cap, prev_count.data_ptr(), 1,
+                                           BN.RATIO, 1, b_match.data_ptr(), b_mcount.data_ptr(), sptr))
+
+    def job(steps):
+        reqs = []
+        for s in range(steps):
+            step(first=(s == 0))
+            if s == 0:
+                reqs = boundary_exchange()
+        for r in reqs:
+            r.wait()
+        boundary_match()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up, then the timed region (device events, max over ranks) -----------------
+    job(max(W, 3))
+    barrier()
+    _native.check(orb_status(L, orb))
+    launches0 = L.vslam_launch_count()
+    sampler = BN.ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    prof = np.zeros(24, np.float64)
+    buf = np.zeros(24, np.float32)
+    L.vslam_orb_set_profiling(orb.handle, 1)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    reqs = []
+    for s in range(K):
+        step(first=(s == 0))
+        if s == 0:
+            reqs = boundary_exchange()
+        _native.check(L.vslam_orb_read_profile(orb.handle, _native.ptr(buf), 24))   # waits for this step
+        prof += buf
+    for r in reqs:
+        r.wait()
+    boundary_match()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    L.vslam_orb_set_profiling(orb.handle, 0)
+    launches = L.vslam_launch_count() - launches0
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * B * K / (ms * 1e-3)
+    n_kp = int(count.clamp(max=cap).sum().item())
+    n_match = int(mcount.sum().item())
+
+    # ---- e2e through the host-buffer C ABI (pinned host memory, copies timed) -----------
+    pin_frames = torch.from_numpy(host_frames).pin_memory()
+    out_kp = torch.empty((B, cap, 6), dtype=torch.float32).pin_memory()
+    out_desc = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    out_count = torch.empty(B, dtype=torch.int32).pin_memory()
+    out_match = torch.empty((B, cap, 3), dtype=torch.int32).pin_memory()
+    out_mcount = torch.empty(B, dtype=torch.int32).pin_memory()
+
+    def e2e_step():
+        _native.check(L.vslam_frontend_run_host(orb.handle, pin_frames.data_ptr(), B, BN.RATIO,
+                                                out_kp.data_ptr(), out_desc.data_ptr(), out_count.data_ptr(),
+                                                out_match.data_ptr(), out_mcount.data_ptr()))
+    Ke = max(2, min(K, 5))
+    e2e_step()
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        e2e_step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_fps = world * B * Ke / float(t.item())
+    h2d = B * w * h
+    d2h = B * cap * (24 + 32) + B * 4 + (B - 1) * (cap * 12 + 4)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(BN.ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        level_ms = float(prof[:16].sum())
+        lvl_bytes = BN.level_kernel_bytes(w, h) * B * K
+        achieved = lvl_bytes / (level_ms * 1e-3) / 1e9 if level_ms > 0 else 0.0
+        breakdown = {("level%d" % i): round(float(prof[i]) / K, 4) for i in range(BN.N_LEVELS)}
+        breakdown.update({BN.PROF_NAMES[i]: round(float(prof[i]) / K, 4) for i in BN.PROF_NAMES})
+        pairs_per_s = (float(n_kp) / B) ** 2 * B * K / (prof[19] * 1e-3) if prof[19] > 0 else 0.0
+        line = {
+            "metric": BN.METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": BN.workload_name(args.workload), "frames_per_step_per_gpu": B,
+                       "l2_policy": "inputs larger than L2 (%.0f MB of frames per step)" % (B * w * h / 1e6),
+                       "sharding": "contiguous frame ranges, 1 boundary descriptor block per rank boundary",
+                       "keypoints_per_frame": n_kp / B, "matches_last_step": n_match},
+            "clocks": clocks,
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": Ke},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "vs_level_kernel (fused pyramid+FAST+NMS+blur, %d launches/step)" % BN.N_LEVELS,
+                         "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "algorithmic_bytes_per_frame": BN.level_kernel_bytes(w, h), "traffic": None,
+                         "ms_per_step": level_ms / K},
+            "extraction": {"ms_per_step": float(prof[:19].sum()) / K,
+                           "algorithmic_bytes_per_frame": BN.extraction_bytes(w, h, nf),
+                           "achieved_gbs": BN.extraction_bytes(w, h, nf) * B * K / (prof[:19].sum() * 1e-3) / 1e9
+                           if prof[:19].sum() > 0 else 0.0},
+            "matching": {"ms_per_step": float(prof[19] + prof[20]) / K, "gpairs_per_s": pairs_per_s / 1e9,
+                         "popc32_per_s": 8 * pairs_per_s},
+            "kernel_ms_per_step": breakdown,
+        }
+        if world == 1 and not args.no_cpu:
+            fps, cores, kind, sample = BN.cpu_front_end_fps(w, h, nf, [host_frames[k] for k in range(min(B, 64))] * 8)
+            line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}
+        print(json.dumps(line), flush=True)
+    orb.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def orb_status(L, orb):
+    return L.vslam_orb_last_status(orb.handle)

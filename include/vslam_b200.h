@@ -42,6 +42,8 @@ const char* vslam_last_error(void);
 int vslam_abi_version(void);
 /* Number of visible CUDA devices (0 when there is no usable driver). */
 int vslam_device_count(void);
+/* Number of CUDA kernels this library has launched in this process so far. */
+unsigned long long vslam_launch_count(void);
 
 /* ------------------------------------------------------------------ extraction */
 
@@ -115,6 +117,14 @@ int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_
 int vslam_gftt_grid_host(const uint8_t* h_frame, int height, int width, int rows, int cols,
                          int max_per_cell, double quality, double min_distance,
                          float* h_xy, int32_t* h_cell_count, int* n_out);
+
+/* Per-kernel timing for bench.py's roofline figures: when enabled, CUDA events are
+ * recorded on the launching stream between the kernels of every call on this handle.
+ * vslam_orb_read_profile waits for the last call and returns its milliseconds per slot:
+ * [0..15] fused level kernel per pyramid level, [16] Harris, [17] select, [18] describe,
+ * [19] kNN-2 (+ merge), [20] ratio filter; n_slots must be >= 24. */
+int vslam_orb_set_profiling(vslam_orb* orb, int enable);
+int vslam_orb_read_profile(vslam_orb* orb, float* h_ms, int n_slots);
 
 /* Debug/test taps used by the stage-wise parity tests: copy pyramid level `level`
  * of frame `frame` of the last batch (raw or blurred) to the host, tightly packed. */

@@ -10,6 +10,8 @@
 #include "common.cuh"
 
 static thread_local char g_err[512] = "";
+unsigned long long g_vs_launches = 0;
+extern "C" unsigned long long vslam_launch_count(void) { return g_vs_launches; }
 
 void vs_set_error(const char* fmt, ...)
 {
@@ -185,6 +187,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
                     o->d_knn_dist, o->d_frames, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
+    for (cudaEvent_t e : o->prof_ev) if (e) cudaEventDestroy(e);
     delete o;
     return VSLAM_OK;
 }
@@ -216,6 +219,7 @@ extern "C" int vslam_orb_detect_and_compute(vslam_orb* o, const uint8_t* d_frame
     o->last_frames = d_frames;
     o->last_pitch = pitch;
     o->last_batch = batch;
+    o->prof_count = 0;
     int rc = vs_launch_levels(o, d_frames, batch, pitch, s);
     if (rc) return rc;
     return vs_launch_select(o, d_frames, batch, pitch, d_kp, d_desc, d_count, s);
@@ -285,5 +289,28 @@ extern "C" int vslam_orb_debug_run_levels_host(vslam_orb* o, const uint8_t* h_fr
     rc = vs_launch_levels(o, o->d_frames, batch, p.width, s);
     if (rc) return rc;
     VS_CUDA(cudaStreamSynchronize(s));
+    return VSLAM_OK;
+}
+
+extern "C" int vslam_orb_set_profiling(vslam_orb* o, int enable)
+{
+    VS_REQUIRE(o, "null handle");
+    o->prof_on = enable ? 1 : 0;
+    o->prof_count = 0;
+    return VSLAM_OK;
+}
+
+extern "C" int vslam_orb_read_profile(vslam_orb* o, float* h_ms, int n_slots)
+{
+    VS_REQUIRE(o && h_ms && n_slots >= VS_PROF_SLOTS, "need room for 24 slots");
+    for (int i = 0; i < n_slots; ++i) h_ms[i] = 0.f;
+    if (o->prof_count < 2) return VSLAM_OK;
+    VS_CUDA(cudaEventSynchronize(o->prof_ev[o->prof_count - 1]));
+    for (int i = 0; i + 1 < o->prof_count; ++i) {
+        if (o->prof_slot[i] < 0) continue;
+        float ms = 0.f;
+        VS_CUDA(cudaEventElapsedTime(&ms, o->prof_ev[i], o->prof_ev[i + 1]));
+        h_ms[o->prof_slot[i]] += ms;
+    }
     return VSLAM_OK;
 }

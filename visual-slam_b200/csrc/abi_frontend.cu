@@ -16,7 +16,7 @@ extern "C" int vslam_bf_knn2_hamming256(const uint8_t* d_query, int nq, long q_s
     if (pairs == 0 || nq == 0) return VSLAM_OK;
     VS_REQUIRE(d_query && d_idx && d_dist && (d_train || nt == 0), "null argument");
     VS_REQUIRE(((uintptr_t)d_query & 15) == 0 && ((uintptr_t)d_train & 15) == 0, "descriptors must be 16-byte aligned");
-    return vs_launch_knn2(d_query, nq, q_stride_rows, d_train, nt, t_stride_rows, d_nq, d_nt, pairs,
+    return vs_launch_knn2(nullptr, d_query, nq, q_stride_rows, d_train, nt, t_stride_rows, d_nq, d_nt, pairs,
                           d_idx, d_dist, (cudaStream_t)stream);
 }
 
@@ -26,7 +26,7 @@ extern "C" int vslam_ratio_filter(const int32_t* d_idx, const int32_t* d_dist, i
 {
     VS_REQUIRE(pairs >= 0 && nq >= 0, "negative size");
     VS_REQUIRE(d_match_count && (nq == 0 || (d_idx && d_dist && d_match)), "null argument");
-    return vs_launch_ratio(d_idx, d_dist, nq, d_nq, pairs, ratio, ratio_test, d_match, d_match_count,
+    return vs_launch_ratio(nullptr, d_idx, d_dist, nq, d_nq, pairs, ratio, ratio_test, d_match, d_match_count,
                            (cudaStream_t)stream);
 }
 
@@ -51,7 +51,7 @@ extern "C" int vslam_bf_knn2_hamming256_host(const uint8_t* h_query, int nq, con
         return rc;
     VS_CUDA(cudaMemcpy(q.p, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
     if (nt) VS_CUDA(cudaMemcpy(t.p, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
-    rc = vs_launch_knn2((const uint8_t*)q.p, nq, nq, (const uint8_t*)t.p, nt, nt, nullptr, nullptr, 1,
+    rc = vs_launch_knn2(nullptr, (const uint8_t*)q.p, nq, nq, (const uint8_t*)t.p, nt, nt, nullptr, nullptr, 1,
                         (int32_t*)i.p, (int32_t*)d.p, 0);
     if (rc) return rc;
     VS_CUDA(cudaMemcpy(h_idx, i.p, (size_t)nq * 8, cudaMemcpyDeviceToHost));
@@ -100,22 +100,23 @@ extern "C" int vslam_frontend_run(vslam_orb* o, const uint8_t* d_frames, int bat
     int32_t* mc = d_match_count;
     if (d_prev_desc) {
         // pair 0 = (previous boundary frame, frame 0)
-        rc = vs_launch_knn2(d_prev_desc, cap, cap, d_desc, cap, cap, d_prev_count, d_count, 1,
+        rc = vs_launch_knn2(o, d_prev_desc, cap, cap, d_desc, cap, cap, d_prev_count, d_count, 1,
                             o->d_knn_idx, o->d_knn_dist, s);
         if (rc) return rc;
-        rc = vs_launch_ratio(o->d_knn_idx, o->d_knn_dist, cap, d_prev_count, 1, ratio, 1, m, mc, s);
+        rc = vs_launch_ratio(o, o->d_knn_idx, o->d_knn_dist, cap, d_prev_count, 1, ratio, 1, m, mc, s);
         if (rc) return rc;
         m += (size_t)cap * 3;
         mc += 1;
     }
     if (batch > 1) {
         // pair i = (frame i, frame i+1): the train block is the query block shifted by one frame
-        rc = vs_launch_knn2(d_desc, cap, cap, d_desc + (size_t)cap * 32, cap, cap, d_count, d_count + 1,
+        rc = vs_launch_knn2(o, d_desc, cap, cap, d_desc + (size_t)cap * 32, cap, cap, d_count, d_count + 1,
                             batch - 1, o->d_knn_idx, o->d_knn_dist, s);
         if (rc) return rc;
-        rc = vs_launch_ratio(o->d_knn_idx, o->d_knn_dist, cap, d_count, batch - 1, ratio, 1, m, mc, s);
+        rc = vs_launch_ratio(o, o->d_knn_idx, o->d_knn_dist, cap, d_count, batch - 1, ratio, 1, m, mc, s);
         if (rc) return rc;
     }
+    vs_prof_mark(o, -1, s);
     return VSLAM_OK;
 }
 

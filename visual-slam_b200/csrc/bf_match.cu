@@ -128,7 +128,7 @@ __global__ void vs_knn2_merge_kernel(const int4* __restrict__ partial, int nq_ma
 static int4* g_partial = nullptr;
 static size_t g_partial_bytes = 0;
 
-int vs_launch_knn2(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
+int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
                    long t_stride, const int32_t* d_nq, const int32_t* d_nt, int pairs,
                    int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
 {
@@ -151,11 +151,15 @@ int vs_launch_knn2(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t
             g_partial_bytes = need;
         }
     }
+    vs_prof_mark(prof, VS_PROF_KNN2, s);
+    ++g_vs_launches;
     vs_knn2_kernel<<<dim3(qtiles, nsplit, pairs), BF_THREADS, 0, s>>>(
         d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, g_partial, d_idx, d_dist);
-    if (nsplit > 1)
+    if (nsplit > 1) {
+        ++g_vs_launches;
         vs_knn2_merge_kernel<<<dim3((nq + 255) / 256, pairs), 256, 0, s>>>(g_partial, nq, d_nq, nsplit,
                                                                           d_idx, d_dist);
+    }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
 }
@@ -204,11 +208,13 @@ vs_ratio_kernel(const int32_t* __restrict__ idx, const int32_t* __restrict__ dis
     if (tid == 0) match_count[pair] = s_base;
 }
 
-int vs_launch_ratio(const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
+int vs_launch_ratio(vslam_orb* prof, const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
                     int pairs, double ratio, int ratio_test, int32_t* d_match,
                     int32_t* d_match_count, cudaStream_t s)
 {
     if (pairs <= 0) return VSLAM_OK;
+    vs_prof_mark(prof, VS_PROF_RATIO, s);
+    ++g_vs_launches;
     vs_ratio_kernel<<<pairs, 256, 0, s>>>(d_idx, d_dist, nq, d_nq, ratio, ratio_test, d_match, d_match_count);
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
@@ -247,6 +253,7 @@ int vs_launch_match_masked(const uint8_t* d_q, int nq, const uint8_t* d_t, int n
                            int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
 {
     if (nq <= 0) return VSLAM_OK;
+    ++g_vs_launches;
     vs_match_masked_kernel<<<(nq + 7) / 8, 256, 0, s>>>(d_q, nq, d_t, nt, d_mask, d_idx, d_dist);
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;

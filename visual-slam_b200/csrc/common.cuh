@@ -17,6 +17,7 @@
 #define VS_TH 32
 #define VS_HALO 4
 
+extern unsigned long long g_vs_launches;   // kernels launched by this library (bench.py reports it)
 void vs_set_error(const char* fmt, ...);
 int vs_cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
@@ -64,6 +65,15 @@ struct VsPlan {
     size_t stage_frame_entries;
 };
 
+// profiling slots: 0..15 level kernels, then the per-keypoint kernels and matching
+#define VS_PROF_HARRIS 16
+#define VS_PROF_SELECT 17
+#define VS_PROF_DESCRIBE 18
+#define VS_PROF_KNN2 19
+#define VS_PROF_RATIO 20
+#define VS_PROF_SLOTS 24
+#define VS_PROF_MAX_MARKS 64
+
 struct vslam_orb {
     vslam_orb_params prm;
     VsPlan plan;
@@ -90,6 +100,10 @@ struct vslam_orb {
     cudaStream_t last_stream;
     const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)
     int last_pitch, last_batch;
+    // optional per-kernel timing (vslam_orb_set_profiling): events recorded between launches
+    int prof_on, prof_count;
+    cudaEvent_t prof_ev[VS_PROF_MAX_MARKS];
+    int prof_slot[VS_PROF_MAX_MARKS];
 };
 
 // counters per (frame, level): [0] candidates, [1] survivors of cut 1, [2] final count,
@@ -104,12 +118,22 @@ struct vslam_orb {
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
-int vs_launch_knn2(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
+int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
                    long t_stride, const int32_t* d_nq, const int32_t* d_nt, int pairs,
                    int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
-int vs_launch_ratio(const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
+int vs_launch_ratio(vslam_orb* prof, const int32_t* d_idx, const int32_t* d_dist, int nq, const int32_t* d_nq,
                     int pairs, double ratio, int ratio_test, int32_t* d_match,
                     int32_t* d_match_count, cudaStream_t s);
+
+// record a timing mark: the time from this mark to the next one is attributed to `slot`
+// (slot < 0 = end of the run)
+static inline void vs_prof_mark(vslam_orb* o, int slot, cudaStream_t s)
+{
+    if (!o || !o->prof_on || o->prof_count >= VS_PROF_MAX_MARKS) return;
+    if (!o->prof_ev[o->prof_count]) cudaEventCreate(&o->prof_ev[o->prof_count]);
+    cudaEventRecord(o->prof_ev[o->prof_count], s);
+    o->prof_slot[o->prof_count++] = slot;
+}
 
 __host__ __device__ inline int vs_reflect101(int i, int n)
 {

@@ -65,7 +65,7 @@ __device__ __forceinline__ int fast_score(const uint8_t* p, int thr)
     }
     // NOTE: max(best, max(mn, -mx)) per arc is miscompiled by ptxas 12.9 (and the 580 driver
     // JIT) for sm_100a: the negation is dropped when the chain is fused into VIMNMX3
-    // (scratch/ft4.cu reproduces it).  Keep the two reductions apart and negate once,
+    // (tools/repro/ptxas_vimnmx3_neg.cu reproduces it).  Keep the two reductions apart and negate once,
     // behind an opaque barrier.
     int best_lo = -256, best_hi = 256;
 #pragma unroll
@@ -249,6 +249,8 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
         const VsLevel& L = p.lv[l];
         if (L.w <= 0 || L.h <= 0) continue;
         dim3 grid(L.tiles_x, L.tiles_y, batch);
+        vs_prof_mark(o, l, s);
+        ++g_vs_launches;
         vs_level_kernel<<<grid, 256, 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height,
                                              o->d_pyr, o->d_tab, o->d_cand, o->d_counters);
     }

@@ -53,6 +53,9 @@ def lib():
         L.vslam_ratio_filter.argtypes = [vp, vp, i32, vp, i32, f64, i32, vp, vp, vp]
         L.vslam_frontend_run.argtypes = [vp, vp, i32, i32, vp, vp, f64, vp, vp, vp, vp, vp, vp]
         L.vslam_frontend_run_host.argtypes = [vp, vp, i32, f64, vp, vp, vp, vp, vp]
+        L.vslam_orb_set_profiling.argtypes = [vp, i32]
+        L.vslam_orb_read_profile.argtypes = [vp, vp, i32]
+        L.vslam_launch_count.restype = C.c_ulonglong
         for name, args in _OPTIONAL.items():
             if hasattr(L, name):
                 getattr(L, name).argtypes = args(vp, i32, f64)
