@@ -1,0 +1,378 @@
+// geom.cu -- RANSAC fundamental / essential matrix, pose recovery and triangulation.
+//
+// Replaces, for the reference's call sites, the OpenCV calib3d entry points
+//   cv2.findFundamentalMat(p1, p2, FM_RANSAC, thr, 0.99)      matcher.py:192, local_mapper.py:136
+//   cv2.findEssentialMat(p1, p2, K, RANSAC, prob, thr)        utils.py:124-125, tracker.py:242
+//   cv2.recoverPose(E, p1, p2, K, mask)                       utils.py:133, tracker.py:249
+//   cv2.triangulatePoints(P1, P2, p1.T, p2.T)                 utils.py:59
+// Scoring follows OpenCV's error functions exactly: F scores with
+// max(d1^2, d2^2) of the two point-to-epipolar-line distances, E with the Sampson error in
+// K-normalised coordinates; both in double, rounded to float and compared with (float)thr^2.
+// Hypotheses: every RANSAC iteration is one thread (7-point / 5-point minimal solver on a
+// sample drawn from a counter-based generator), every model is scored by one CTA, and the
+// host replays OpenCV's sequential adaptive-termination rule over the per-model inlier counts,
+// so the result is deterministic for a given seed.
+#include <float.h>
+#include <math.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "geom_5pt.cuh"
+
+namespace {
+
+struct DevMem {
+    void* p = nullptr;
+    ~DevMem() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
+    template <class T> T* as() { return (T*)p; }
+};
+
+__host__ __device__ inline uint64_t mix64(uint64_t x)
+{
+    x += 0x9e3779b97f4a7c15ull;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    return x ^ (x >> 31);
+}
+
+// k distinct indices in [0, n) for RANSAC iteration `it` (duplicate rejection, like cv::RNG sampling)
+template <int K>
+__device__ inline void draw_sample(uint64_t seed, int it, int n, int idx[K])
+{
+    uint64_t ctr = 0;
+    for (int j = 0; j < K;) {
+        uint64_t r = mix64(seed ^ mix64(((uint64_t)it << 20) + ctr));
+        ++ctr;
+        int v = (int)(r % (uint64_t)n);
+        bool dup = false;
+        for (int t = 0; t < j; ++t) dup |= idx[t] == v;
+        if (!dup) idx[j++] = v;
+    }
+}
+
+// OpenCV's FMEstimatorCallback::computeError for one correspondence (double, then float)
+__device__ __forceinline__ float f_error(const double* F, float x1, float y1, float x2, float y2)
+{
+    double a = F[0] * x1 + F[1] * y1 + F[2];
+    double b = F[3] * x1 + F[4] * y1 + F[5];
+    double c = F[6] * x1 + F[7] * y1 + F[8];
+    double s2 = 1. / (a * a + b * b);
+    double d2 = x2 * a + y2 * b + c;
+    a = F[0] * x2 + F[3] * y2 + F[6];
+    b = F[1] * x2 + F[4] * y2 + F[7];
+    c = F[2] * x2 + F[5] * y2 + F[8];
+    double s1 = 1. / (a * a + b * b);
+    double d1 = x1 * a + y1 * b + c;
+    return (float)fmax(d1 * d1 * s1, d2 * d2 * s2);
+}
+
+// OpenCV's EMEstimatorCallback::computeError (Sampson) on normalised double coordinates
+__device__ __forceinline__ float e_error(const double* E, double x1, double y1, double x2, double y2)
+{
+    double Ex0 = E[0] * x1 + E[1] * y1 + E[2];
+    double Ex1 = E[3] * x1 + E[4] * y1 + E[5];
+    double Ex2 = E[6] * x1 + E[7] * y1 + E[8];
+    double Et0 = E[0] * x2 + E[3] * y2 + E[6];
+    double Et1 = E[1] * x2 + E[4] * y2 + E[7];
+    double x2tEx1 = x2 * Ex0 + y2 * Ex1 + Ex2;
+    double a = Ex0 * Ex0, b = Ex1 * Ex1, c = Et0 * Et0, d = Et1 * Et1;
+    return (float)(x2tEx1 * x2tEx1 / (a + b + c + d));
+}
+
+// ---- scoring: one CTA per model -----------------------------------------------------------
+// mode 0: fundamental (float2 points), mode 1: essential (double2 normalised points)
+template <int MODE>
+__global__ void __launch_bounds__(128)
+vs_score_models_kernel(const double* __restrict__ models, const int* __restrict__ n_models, int per_iter,
+                       const void* __restrict__ p1v, const void* __restrict__ p2v, int n, float thr2,
+                       int* __restrict__ counts, uint8_t* __restrict__ mask)
+{
+    const int m = blockIdx.x;
+    if (n_models && (m % per_iter) >= n_models[m / per_iter]) {
+        if (threadIdx.x == 0 && counts) counts[m] = -1;
+        return;
+    }
+    __shared__ double M[9];
+    __shared__ int s_cnt;
+    if (threadIdx.x < 9) M[threadIdx.x] = models[(size_t)m * 9 + threadIdx.x];
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    int cnt = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        float err;
+        if (MODE == 0) {
+            const float2 a = ((const float2*)p1v)[i], b = ((const float2*)p2v)[i];
+            err = f_error(M, a.x, a.y, b.x, b.y);
+        } else {
+            const double2 a = ((const double2*)p1v)[i], b = ((const double2*)p2v)[i];
+            err = e_error(M, a.x, a.y, b.x, b.y);
+        }
+        const int in = err <= thr2;
+        cnt += in;
+        if (mask) mask[i] = (uint8_t)in;
+    }
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    if (threadIdx.x == 0 && counts) counts[m] = s_cnt;
+}
+
+// ---- hypotheses -------------------------------------------------------------------------
+// Hartley normalisation of one point set: x' = (x - cx) * s
+struct Norm2 { double cx, cy, s; };
+
+__global__ void vs_ransac_f_hyp_kernel(const float2* __restrict__ p1, const float2* __restrict__ p2, int n,
+                                       Norm2 n1, Norm2 n2, uint64_t seed, int iters,
+                                       double* __restrict__ models, int* __restrict__ n_models)
+{
+    const int it = blockIdx.x * blockDim.x + threadIdx.x;
+    if (it >= iters) return;
+    int idx[7];
+    draw_sample<7>(seed, it, n, idx);
+    double x1[7][2], x2[7][2];
+    for (int j = 0; j < 7; ++j) {
+        float2 a = p1[idx[j]], b = p2[idx[j]];
+        x1[j][0] = (a.x - n1.cx) * n1.s; x1[j][1] = (a.y - n1.cy) * n1.s;
+        x2[j][0] = (b.x - n2.cx) * n2.s; x2[j][1] = (b.y - n2.cy) * n2.s;
+    }
+    double F[3][9];
+    const int nf = solve_7pt(x1, x2, F);
+    int kept = 0;
+    for (int k = 0; k < nf; ++k) {
+        // denormalise: F = T2^T Fn T1 with T = [s 0 -s cx; 0 s -s cy; 0 0 1]
+        const double* f = F[k];
+        double A[9];   // Fn * T1
+        for (int r = 0; r < 3; ++r) {
+            A[3 * r] = f[3 * r] * n1.s;
+            A[3 * r + 1] = f[3 * r + 1] * n1.s;
+            A[3 * r + 2] = f[3 * r + 2] - n1.s * (f[3 * r] * n1.cx + f[3 * r + 1] * n1.cy);
+        }
+        double G[9];   // T2^T * A
+        for (int c = 0; c < 3; ++c) {
+            G[c] = n2.s * A[c];
+            G[3 + c] = n2.s * A[3 + c];
+            G[6 + c] = A[6 + c] - n2.s * (n2.cx * A[c] + n2.cy * A[3 + c]);
+        }
+        bool ok = true;
+        for (int e = 0; e < 9; ++e) ok &= isfinite(G[e]);
+        if (!ok) continue;
+        const double mu = fabs(G[8]) > DBL_EPSILON ? 1.0 / G[8] : 1.0;    // F[2][2] = 1 as OpenCV's run7Point
+        double* out = models + ((size_t)it * 3 + kept) * 9;
+        for (int e = 0; e < 9; ++e) out[e] = G[e] * mu;
+        ++kept;
+    }
+    n_models[it] = kept;
+}
+
+__global__ void vs_ransac_e_hyp_kernel(const double2* __restrict__ p1, const double2* __restrict__ p2, int n,
+                                       uint64_t seed, int iters, double* __restrict__ models,
+                                       int* __restrict__ n_models)
+{
+    const int it = blockIdx.x * blockDim.x + threadIdx.x;
+    if (it >= iters) return;
+    int idx[5];
+    draw_sample<5>(seed, it, n, idx);
+    double x1[5][2], x2[5][2];
+    for (int j = 0; j < 5; ++j) {
+        double2 a = p1[idx[j]], b = p2[idx[j]];
+        x1[j][0] = a.x; x1[j][1] = a.y; x2[j][0] = b.x; x2[j][1] = b.y;
+    }
+    double E[10][9];
+    const int ne = solve_5pt(x1, x2, E);
+    for (int k = 0; k < ne; ++k)
+        for (int e = 0; e < 9; ++e) models[((size_t)it * 10 + k) * 9 + e] = E[k][e];
+    n_models[it] = ne;
+}
+
+// cv::RANSACUpdateNumIters
+int ransac_update_iters(double p, double ep, int model_points, int max_iters)
+{
+    p = fmax(p, 0.); p = fmin(p, 1.);
+    ep = fmax(ep, 0.); ep = fmin(ep, 1.);
+    double num = fmax(1. - p, DBL_MIN);
+    double denom = 1. - pow(1. - ep, model_points);
+    if (denom < DBL_MIN) return 0;
+    num = log(num);
+    denom = log(denom);
+    return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)lrint(num / denom);
+}
+
+// Replays OpenCV's sequential RANSAC loop over per-model inlier counts; returns the winning
+// model index (iteration * per_iter + k) or -1.
+int ransac_replay(const std::vector<int>& counts, const std::vector<int>& n_models, int per_iter, int n,
+                  int model_points, double conf, int max_iters)
+{
+    int niters = max_iters, max_good = 0, best = -1;
+    for (int it = 0; it < niters && it < (int)n_models.size(); ++it)
+        for (int k = 0; k < n_models[it]; ++k) {
+            const int good = counts[(size_t)it * per_iter + k];
+            if (good > (max_good > model_points - 1 ? max_good : model_points - 1)) {
+                best = it * per_iter + k;
+                max_good = good;
+                niters = ransac_update_iters(conf, (double)(n - good) / n, model_points, niters);
+            }
+        }
+    return best;
+}
+
+}  // namespace
+
+#define GEOM_CUDA(call)                                                                  \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) return vs_cuda_fail(e__, #call, __FILE__, __LINE__);     \
+    } while (0)
+
+static int score_common(int mode, const double* h_M, const void* d_p1, const void* d_p2, int n, float thr2,
+                        uint8_t* h_mask, int* n_inliers)
+{
+    DevMem m, cnt, mask;
+    GEOM_CUDA(m.alloc(9 * sizeof(double)));
+    GEOM_CUDA(cnt.alloc(sizeof(int)));
+    GEOM_CUDA(mask.alloc(n));
+    GEOM_CUDA(cudaMemcpy(m.p, h_M, 9 * sizeof(double), cudaMemcpyHostToDevice));
+    ++g_vs_launches;
+    if (mode == 0)
+        vs_score_models_kernel<0><<<1, 128>>>(m.as<double>(), nullptr, 1, d_p1, d_p2, n, thr2, cnt.as<int>(), mask.as<uint8_t>());
+    else
+        vs_score_models_kernel<1><<<1, 128>>>(m.as<double>(), nullptr, 1, d_p1, d_p2, n, thr2, cnt.as<int>(), mask.as<uint8_t>());
+    GEOM_CUDA(cudaGetLastError());
+    int c = 0;
+    GEOM_CUDA(cudaMemcpy(&c, cnt.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, mask.p, n, cudaMemcpyDeviceToHost));
+    if (n_inliers) *n_inliers = c;
+    return VSLAM_OK;
+}
+
+static void normalise_points(const float* p, int n, const double* K, std::vector<double>& out)
+{
+    // cv::findEssentialMat / recoverPose: double points, (x - cx) / fx, (y - cy) / fy
+    const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+    out.resize((size_t)2 * n);
+    for (int i = 0; i < n; ++i) {
+        out[2 * i] = ((double)p[2 * i] - cx) / fx;
+        out[2 * i + 1] = ((double)p[2 * i + 1] - cy) / fy;
+    }
+}
+
+extern "C" int vslam_score_fundamental_host(const double* h_F, const float* h_p1, const float* h_p2, int n,
+                                            double thr, uint8_t* h_mask, int* n_inliers)
+{
+    VS_REQUIRE(h_F && h_p1 && h_p2 && n >= 0, "bad argument");
+    if (n_inliers) *n_inliers = 0;
+    if (n == 0) return VSLAM_OK;
+    DevMem a, b;
+    GEOM_CUDA(a.alloc((size_t)n * 8));
+    GEOM_CUDA(b.alloc((size_t)n * 8));
+    GEOM_CUDA(cudaMemcpy(a.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(b.p, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    return score_common(0, h_F, a.p, b.p, n, (float)(thr * thr), h_mask, n_inliers);
+}
+
+extern "C" int vslam_score_essential_host(const double* h_E, const double* h_K, const float* h_p1,
+                                          const float* h_p2, int n, double thr, uint8_t* h_mask, int* n_inliers)
+{
+    VS_REQUIRE(h_E && h_K && h_p1 && h_p2 && n >= 0, "bad argument");
+    if (n_inliers) *n_inliers = 0;
+    if (n == 0) return VSLAM_OK;
+    std::vector<double> q1, q2;
+    normalise_points(h_p1, n, h_K, q1);
+    normalise_points(h_p2, n, h_K, q2);
+    DevMem a, b;
+    GEOM_CUDA(a.alloc((size_t)n * 16));
+    GEOM_CUDA(b.alloc((size_t)n * 16));
+    GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+    double t = thr / ((h_K[0] + h_K[4]) / 2);
+    return score_common(1, h_E, a.p, b.p, n, (float)(t * t), h_mask, n_inliers);
+}
+
+static Norm2 hartley(const float* p, int n)
+{
+    double cx = 0, cy = 0;
+    for (int i = 0; i < n; ++i) { cx += p[2 * i]; cy += p[2 * i + 1]; }
+    cx /= n; cy /= n;
+    double d = 0;
+    for (int i = 0; i < n; ++i) d += hypot(p[2 * i] - cx, p[2 * i + 1] - cy);
+    d /= n;
+    Norm2 r = {cx, cy, d > 0 ? sqrt(2.0) / d : 1.0};
+    return r;
+}
+
+// shared driver: hypotheses -> per-model counts -> sequential replay -> final mask
+static int ransac_driver(int mode, const void* d_p1, const void* d_p2, int n, const float* h_p1, const float* h_p2,
+                         float thr2, double conf, int max_iters, uint64_t seed, double* h_model, uint8_t* h_mask,
+                         int* n_inliers)
+{
+    const int per = mode == 0 ? 3 : 10, mp = mode == 0 ? 7 : 5;
+    DevMem models, nm, counts;
+    GEOM_CUDA(models.alloc((size_t)max_iters * per * 9 * sizeof(double)));
+    GEOM_CUDA(nm.alloc((size_t)max_iters * sizeof(int)));
+    GEOM_CUDA(counts.alloc((size_t)max_iters * per * sizeof(int)));
+    ++g_vs_launches;
+    if (mode == 0) {
+        Norm2 n1 = hartley(h_p1, n), n2 = hartley(h_p2, n);
+        vs_ransac_f_hyp_kernel<<<(max_iters + 63) / 64, 64>>>((const float2*)d_p1, (const float2*)d_p2, n, n1, n2, seed,
+                                                            max_iters, models.as<double>(), nm.as<int>());
+    } else {
+        vs_ransac_e_hyp_kernel<<<(max_iters + 31) / 32, 32>>>((const double2*)d_p1, (const double2*)d_p2, n, seed,
+                                                            max_iters, models.as<double>(), nm.as<int>());
+    }
+    GEOM_CUDA(cudaGetLastError());
+    ++g_vs_launches;
+    if (mode == 0)
+        vs_score_models_kernel<0><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
+                                                           counts.as<int>(), nullptr);
+    else
+        vs_score_models_kernel<1><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
+                                                           counts.as<int>(), nullptr);
+    GEOM_CUDA(cudaGetLastError());
+    std::vector<int> h_counts((size_t)max_iters * per), h_nm(max_iters);
+    GEOM_CUDA(cudaMemcpy(h_counts.data(), counts.p, h_counts.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    GEOM_CUDA(cudaMemcpy(h_nm.data(), nm.p, h_nm.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    const int best = ransac_replay(h_counts, h_nm, per, n, mp, conf, max_iters);
+    if (n_inliers) *n_inliers = 0;
+    if (best < 0) {
+        for (int e = 0; e < 9; ++e) h_model[e] = 0.0;
+        if (h_mask) memset(h_mask, 0, n);
+        return VSLAM_OK;
+    }
+    GEOM_CUDA(cudaMemcpy(h_model, models.as<double>() + (size_t)best * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+    return score_common(mode, h_model, d_p1, d_p2, n, thr2, h_mask, n_inliers);
+}
+
+extern "C" int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p2, int n, double thr, double conf,
+                                             int max_iters, uint64_t seed, double* h_F, uint8_t* h_mask,
+                                             int* n_inliers)
+{
+    VS_REQUIRE(h_p1 && h_p2 && h_F, "null argument");
+    VS_REQUIRE(n >= 7, "need at least 7 correspondences");
+    VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
+    DevMem a, b;
+    GEOM_CUDA(a.alloc((size_t)n * 8));
+    GEOM_CUDA(b.alloc((size_t)n * 8));
+    GEOM_CUDA(cudaMemcpy(a.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(b.p, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    return ransac_driver(0, a.p, b.p, n, h_p1, h_p2, (float)(thr * thr), conf, max_iters, seed, h_F, h_mask, n_inliers);
+}
+
+extern "C" int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, const double* h_K,
+                                           double prob, double thr, int max_iters, uint64_t seed, double* h_E,
+                                           uint8_t* h_mask, int* n_inliers)
+{
+    VS_REQUIRE(h_p1 && h_p2 && h_K && h_E, "null argument");
+    VS_REQUIRE(n >= 5, "need at least 5 correspondences");
+    VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
+    std::vector<double> q1, q2;
+    normalise_points(h_p1, n, h_K, q1);
+    normalise_points(h_p2, n, h_K, q2);
+    DevMem a, b;
+    GEOM_CUDA(a.alloc((size_t)n * 16));
+    GEOM_CUDA(b.alloc((size_t)n * 16));
+    GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
+    double t = thr / ((h_K[0] + h_K[4]) / 2);
+    return ransac_driver(1, a.p, b.p, n, nullptr, nullptr, (float)(t * t), prob, max_iters, seed, h_E, h_mask, n_inliers);
+}

@@ -1,0 +1,260 @@
+// geom_5pt.cuh -- 5-point essential-matrix solver (Nister 2004) and small Jacobi SVDs.
+#pragma once
+#include "geom_solvers.cuh"
+#include "geom_tables.inc"
+
+// ---- polynomial helpers in (x, y, z, 1): linear = 4, quadratic = 10, cubic = 20 coeffs ----
+VS_HD inline void poly_mul_ll(const double* a, const double* b, double* q, double s)   // q += s*a*b
+{
+    const signed char QI[4][4] = VS_QIDX_INIT;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) q[QI[i][j]] += s * a[i] * b[j];
+}
+VS_HD inline void poly_mul_ql(const double* q, const double* l, double* c, double s)   // c += s*q*l
+{
+    const signed char CQ[10][4] = VS_CQ_INIT;
+    for (int i = 0; i < 10; ++i)
+        for (int k = 0; k < 4; ++k) c[CQ[i][k]] += s * q[i] * l[k];
+}
+
+// real polynomial helpers (dense, ascending powers)
+VS_HD inline void pmul(const double* a, int da, const double* b, int db, double* out)  // out = a*b
+{
+    for (int i = 0; i <= da + db; ++i) out[i] = 0.0;
+    for (int i = 0; i <= da; ++i)
+        for (int j = 0; j <= db; ++j) out[i + j] += a[i] * b[j];
+}
+
+// Real roots of a degree-10 polynomial (ascending coefficients c[0..10]) by Durand-Kerner in
+// complex double followed by Newton polishing of the near-real roots.  Returns the count.
+VS_HD inline int real_roots_deg10(const double* c, double* roots)
+{
+    const int N = 10;
+    double lead = c[N];
+    double mx = 0.0;
+    for (int i = 0; i <= N; ++i) mx = fmax(mx, fabs(c[i]));
+    if (!(mx > 0.0) || fabs(lead) < 1e-13 * mx) return 0;
+    double a[N + 1];
+    for (int i = 0; i <= N; ++i) a[i] = c[i] / lead;
+    // Cauchy bound for the starting radius
+    double rad = 0.0;
+    for (int i = 0; i < N; ++i) rad = fmax(rad, fabs(a[i]));
+    rad = fmin(1.0 + rad, 1e6);
+    double zr[N], zi[N];
+    for (int k = 0; k < N; ++k) {
+        double ang = 2.0 * 3.14159265358979323846 * k / N + 0.4;
+        zr[k] = 0.5 * rad * cos(ang) * (0.3 + 0.7 * (k + 1) / N);
+        zi[k] = 0.5 * rad * sin(ang) * (0.3 + 0.7 * (k + 1) / N);
+    }
+    for (int it = 0; it < 120; ++it) {
+        double maxd = 0.0;
+        for (int k = 0; k < N; ++k) {
+            // p(z_k) by Horner
+            double pr = 1.0, pi = 0.0;
+            for (int i = N - 1; i >= 0; --i) {
+                double tr = pr * zr[k] - pi * zi[k] + a[i];
+                pi = pr * zi[k] + pi * zr[k];
+                pr = tr;
+            }
+            // q = prod_{j != k} (z_k - z_j)
+            double qr = 1.0, qi = 0.0;
+            for (int j = 0; j < N; ++j) {
+                if (j == k) continue;
+                double dr = zr[k] - zr[j], di = zi[k] - zi[j];
+                double tr = qr * dr - qi * di;
+                qi = qr * di + qi * dr;
+                qr = tr;
+            }
+            double den = qr * qr + qi * qi;
+            if (den < 1e-300) den = 1e-300;
+            double dr = (pr * qr + pi * qi) / den, di = (pi * qr - pr * qi) / den;
+            zr[k] -= dr;
+            zi[k] -= di;
+            maxd = fmax(maxd, fabs(dr) + fabs(di));
+        }
+        if (maxd < 1e-14 * rad) break;
+    }
+    int n = 0;
+    for (int k = 0; k < N; ++k) {
+        if (fabs(zi[k]) > 1e-5 * (1.0 + fabs(zr[k]))) continue;
+        double x = zr[k];
+        for (int it = 0; it < 4; ++it) {          // Newton on the real polynomial
+            double f = a[N], fp = 0.0;
+            for (int i = N - 1; i >= 0; --i) { fp = fp * x + f; f = f * x + a[i]; }
+            if (fp != 0.0 && isfinite(f / fp)) x -= f / fp;
+        }
+        bool dup = false;
+        for (int j = 0; j < n; ++j) dup |= fabs(roots[j] - x) < 1e-9 * (1.0 + fabs(x));
+        if (!dup && isfinite(x)) roots[n++] = x;
+    }
+    return n;
+}
+
+// 5-point solver.  x1, x2: 5 correspondences in normalised camera coordinates.
+// Writes up to 10 essential matrices (row-major, x2^T E x1 = 0); returns the count.
+VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double E[10][9])
+{
+    double A[5][9], nb[4][9];
+    for (int i = 0; i < 5; ++i) {
+        const double u = x1[i][0], v = x1[i][1], up = x2[i][0], vp = x2[i][1];
+        A[i][0] = up * u; A[i][1] = up * v; A[i][2] = up;
+        A[i][3] = vp * u; A[i][4] = vp * v; A[i][5] = vp;
+        A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
+    }
+    null_space_9<5>(A, nb);
+    // entry e = 3*i + j of E as a linear form in (x, y, z, 1)
+    double L[9][4];
+    for (int e = 0; e < 9; ++e)
+        for (int k = 0; k < 4; ++k) L[e][k] = nb[k][e];
+
+    double M[10][20];
+    for (int r = 0; r < 10; ++r)
+        for (int c = 0; c < 20; ++c) M[r][c] = 0.0;
+    double q[10];
+    // row 0: det(E)
+    {
+        const int idx[6][3] = {{0, 4, 8}, {1, 5, 6}, {2, 3, 7}, {2, 4, 6}, {1, 3, 8}, {0, 5, 7}};
+        for (int t = 0; t < 6; ++t) {
+            for (int i = 0; i < 10; ++i) q[i] = 0.0;
+            poly_mul_ll(L[idx[t][0]], L[idx[t][1]], q, 1.0);
+            poly_mul_ql(q, L[idx[t][2]], M[0], t < 3 ? 1.0 : -1.0);
+        }
+    }
+    // EEt (symmetric 3x3 of quadratics) and Lambda = EEt - 0.5 trace I
+    double EEt[3][3][10];
+    for (int i = 0; i < 3; ++i)
+        for (int j = i; j < 3; ++j) {
+            for (int t = 0; t < 10; ++t) EEt[i][j][t] = 0.0;
+            for (int k = 0; k < 3; ++k) poly_mul_ll(L[3 * i + k], L[3 * j + k], EEt[i][j], 1.0);
+            if (j != i)
+                for (int t = 0; t < 10; ++t) EEt[j][i][t] = EEt[i][j][t];
+        }
+    for (int t = 0; t < 10; ++t) {
+        double tr = 0.5 * (EEt[0][0][t] + EEt[1][1][t] + EEt[2][2][t]);
+        EEt[0][0][t] -= tr; EEt[1][1][t] -= tr; EEt[2][2][t] -= tr;
+    }
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            for (int k = 0; k < 3; ++k) poly_mul_ql(EEt[i][k], L[3 * k + j], M[1 + 3 * i + j], 1.0);
+
+    // Gauss-Jordan on the first 10 columns (partial pivoting)
+    for (int c = 0; c < 10; ++c) {
+        int pr = c;
+        double best = fabs(M[c][c]);
+        for (int r = c + 1; r < 10; ++r)
+            if (fabs(M[r][c]) > best) { best = fabs(M[r][c]); pr = r; }
+        if (best < 1e-300) return 0;
+        if (pr != c)
+            for (int j = 0; j < 20; ++j) { double t = M[c][j]; M[c][j] = M[pr][j]; M[pr][j] = t; }
+        double inv = 1.0 / M[c][c];
+        for (int j = c; j < 20; ++j) M[c][j] *= inv;
+        for (int r = 0; r < 10; ++r) {
+            if (r == c) continue;
+            double f = M[r][c];
+            if (f == 0.0) continue;
+            for (int j = c; j < 20; ++j) M[r][j] -= f * M[c][j];
+        }
+    }
+    // B(z): rows k = e - z f, l = g - z h, m = i - z j; columns (x, y, 1) as polynomials in z
+    double B[3][3][5];
+    for (int r = 0; r < 3; ++r) {
+        const double* e = M[4 + 2 * r];
+        const double* f = M[5 + 2 * r];
+        // x column (degree 3): from xz^2 (10), xz (11), x (12)
+        B[r][0][0] = e[12]; B[r][0][1] = e[11] - f[12]; B[r][0][2] = e[10] - f[11]; B[r][0][3] = -f[10]; B[r][0][4] = 0.0;
+        // y column (degree 3): yz^2 (13), yz (14), y (15)
+        B[r][1][0] = e[15]; B[r][1][1] = e[14] - f[15]; B[r][1][2] = e[13] - f[14]; B[r][1][3] = -f[13]; B[r][1][4] = 0.0;
+        // constant column (degree 4): z^3 (16), z^2 (17), z (18), 1 (19)
+        B[r][2][0] = e[19]; B[r][2][1] = e[18] - f[19]; B[r][2][2] = e[17] - f[18]; B[r][2][3] = e[16] - f[17];
+        B[r][2][4] = -f[16];
+    }
+    // det B(z): degree 10
+    double det[11];
+    for (int i = 0; i <= 10; ++i) det[i] = 0.0;
+    {
+        double t1[8], t2[8], minor[8], prod[12];
+        // k_x (l_y m_1 - l_1 m_y)
+        pmul(B[1][1], 3, B[2][2], 4, t1); pmul(B[1][2], 4, B[2][1], 3, t2);
+        for (int i = 0; i <= 7; ++i) minor[i] = t1[i] - t2[i];
+        pmul(B[0][0], 3, minor, 7, prod);
+        for (int i = 0; i <= 10; ++i) det[i] += prod[i];
+        // - k_y (l_x m_1 - l_1 m_x)
+        pmul(B[1][0], 3, B[2][2], 4, t1); pmul(B[1][2], 4, B[2][0], 3, t2);
+        for (int i = 0; i <= 7; ++i) minor[i] = t1[i] - t2[i];
+        pmul(B[0][1], 3, minor, 7, prod);
+        for (int i = 0; i <= 10; ++i) det[i] -= prod[i];
+        // + k_1 (l_x m_y - l_y m_x)
+        pmul(B[1][0], 3, B[2][1], 3, t1); pmul(B[1][1], 3, B[2][0], 3, t2);
+        for (int i = 0; i <= 6; ++i) minor[i] = t1[i] - t2[i];
+        minor[7] = 0.0;
+        pmul(B[0][2], 4, minor, 6, prod);
+        for (int i = 0; i <= 10; ++i) det[i] += prod[i];
+    }
+    double zs[10];
+    const int nz = real_roots_deg10(det, zs);
+    int n = 0;
+    for (int s = 0; s < nz; ++s) {
+        const double z = zs[s];
+        double b[3][3];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) {
+                double v = B[r][c][4];
+                for (int i = 3; i >= 0; --i) v = v * z + B[r][c][i];
+                b[r][c] = v;
+            }
+        // (x, y) from the best-conditioned pair of rows
+        double bestD = 0.0, x = 0.0, y = 0.0;
+        for (int p = 0; p < 3; ++p) {
+            const int r0 = p, r1 = (p + 1) % 3;
+            double D = b[r0][0] * b[r1][1] - b[r0][1] * b[r1][0];
+            if (fabs(D) > fabs(bestD)) {
+                bestD = D;
+                x = (b[r0][1] * b[r1][2] - b[r0][2] * b[r1][1]) / D;
+                y = (b[r0][2] * b[r1][0] - b[r0][0] * b[r1][2]) / D;
+            }
+        }
+        if (bestD == 0.0 || !isfinite(x) || !isfinite(y)) continue;
+        double nrm = 0.0;
+        for (int e = 0; e < 9; ++e) {
+            E[n][e] = x * L[e][0] + y * L[e][1] + z * L[e][2] + L[e][3];
+            nrm += E[n][e] * E[n][e];
+        }
+        if (!(nrm > 0.0) || !isfinite(nrm)) continue;
+        nrm = 1.0 / sqrt(nrm);               // Frobenius norm 1 => singular values (1/sqrt2, 1/sqrt2, 0), as cv2 returns
+        for (int e = 0; e < 9; ++e) E[n][e] *= nrm;
+        ++n;
+    }
+    return n;
+}
+
+// One-sided Jacobi SVD of an N x N matrix A (row-major, overwritten: A <- U diag(s)); V
+// accumulates the right singular vectors in its columns.  Returns nothing; the singular
+// values are the column norms of the result.
+template <int N>
+VS_HD inline void jacobi_svd(double A[N][N], double V[N][N])
+{
+    for (int i = 0; i < N; ++i)
+        for (int j = 0; j < N; ++j) V[i][j] = i == j ? 1.0 : 0.0;
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        double off = 0.0;
+        for (int p = 0; p < N - 1; ++p)
+            for (int q = p + 1; q < N; ++q) {
+                double a = 0.0, b = 0.0, g = 0.0;
+                for (int i = 0; i < N; ++i) { a += A[i][p] * A[i][p]; b += A[i][q] * A[i][q]; g += A[i][p] * A[i][q]; }
+                if (fabs(g) <= 1e-16 * sqrt(a * b) || g == 0.0) continue;
+                off = fmax(off, fabs(g) / sqrt(a * b + 1e-300));
+                double zeta = (b - a) / (2.0 * g);
+                double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
+                for (int i = 0; i < N; ++i) {
+                    double ap = A[i][p], aq = A[i][q];
+                    A[i][p] = cs * ap - sn * aq;
+                    A[i][q] = sn * ap + cs * aq;
+                    double vp = V[i][p], vq = V[i][q];
+                    V[i][p] = cs * vp - sn * vq;
+                    V[i][q] = sn * vp + cs * vq;
+                }
+            }
+        if (off < 1e-15) break;
+    }
+}

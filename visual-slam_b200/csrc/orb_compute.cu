@@ -1,0 +1,126 @@
+// orb_compute.cu -- BGR->gray (K0) and descriptors at caller-supplied keypoints (a3).
+//
+// vslam_bgr2gray_host   replaces cv2.cvtColor(image, COLOR_BGR2GRAY) (extractor.py:62,81,101):
+//                       gray = (B*3735 + G*19235 + R*9798 + 16384) >> 15  
+// vslam_orb_compute_host replaces cv2.ORB.compute(image, keypoints) (extractor.py:83,140):
+//                       border filter on the rounded level-0 point, level-major stable order,
+//                       rBRIEF on the blurred level with the keypoint's OWN angle and octave.
+#include <math.h>
+
+#include <vector>
+
+#include "brief.cuh"
+
+__global__ void vs_bgr2gray_kernel(const uint8_t* __restrict__ bgr, uint8_t* __restrict__ gray, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t* p = bgr + 3 * i;
+    gray[i] = (uint8_t)((p[0] * 3735 + p[1] * 19235 + p[2] * 9798 + 16384) >> 15);
+}
+
+extern "C" int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_gray)
+{
+    VS_REQUIRE(h_bgr && h_gray && height > 0 && width > 0, "bad argument");
+    const size_t n = (size_t)height * width;
+    uint8_t *d_in = nullptr, *d_out = nullptr;
+    VS_CUDA(cudaMalloc(&d_in, 3 * n));
+    cudaError_t e = cudaMalloc(&d_out, n);
+    if (e == cudaSuccess) e = cudaMemcpy(d_in, h_bgr, 3 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        ++g_vs_launches;
+        vs_bgr2gray_kernel<<<(unsigned)((n + 255) / 256), 256>>>(d_in, d_out, n);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(h_gray, d_out, n, cudaMemcpyDeviceToHost);
+    cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    if (e != cudaSuccess) return vs_cuda_fail(e, "bgr2gray", __FILE__, __LINE__);
+    return VSLAM_OK;
+}
+
+struct VsGivenKp { float x, y, angle; int32_t octave; };
+
+// one warp per keypoint; pyramid (raw + blurred levels) of frame 0 of the last level pass
+__global__ void __launch_bounds__(256)
+vs_describe_given_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frame, int fpitch,
+                         const uint8_t* __restrict__ pyr, const VsGivenKp* __restrict__ kps, int n,
+                         uint8_t* __restrict__ desc_out)
+{
+    __shared__ uint32_t s_pat[256];
+    load_pattern(s_pat);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const VsGivenKp k = kps[i];
+    const VsLevel& L = plan.lv[k.octave];
+    const uint8_t* raw;
+    int rpitch;
+    if (k.octave == 0) { raw = frame; rpitch = fpitch; }
+    else { raw = pyr + L.raw_off; rpitch = L.pitch; }
+    const float inv = __fdiv_rn(1.f, L.scale);
+    const int cx = __float2int_rn(__fmul_rn(k.x, inv)), cy = __float2int_rn(__fmul_rn(k.y, inv));
+    const float rad = __fmul_rn(k.angle, (float)(3.14159265358979323846 / 180.f));
+    const float ca = (float)cos((double)rad), sa = (float)sin((double)rad);
+    uint32_t byte = brief_byte(pyr + L.blur_off, raw, L.w, L.h, L.pitch, rpitch, cx, cy, ca, sa, s_pat, lane);
+    desc_out[(size_t)i * 32 + lane] = (uint8_t)byte;
+}
+
+int vs_ensure_host_staging(vslam_orb* o);
+
+extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, const float* h_x, const float* h_y,
+                                      const float* h_angle, const int32_t* h_octave, int n, uint8_t* h_desc,
+                                      int32_t* h_keep_index, int* n_out)
+{
+    VS_REQUIRE(o && h_frame && n_out && n >= 0, "bad argument");
+    *n_out = 0;
+    if (n == 0) return VSLAM_OK;
+    VS_REQUIRE(h_x && h_y && h_angle && h_octave && h_desc && h_keep_index, "null argument");
+    const VsPlan& p = o->plan;
+    // runByImageBorder on the rounded level-0 point, then level-major stable order
+    std::vector<VsGivenKp> kept;
+    std::vector<int32_t> keep_idx;
+    kept.reserve(n);
+    for (int l = 0; l < p.n_levels; ++l)
+        for (int i = 0; i < n; ++i) {
+            if (h_octave[i] != l) continue;
+            const int rx = (int)lrintf(h_x[i]), ry = (int)lrintf(h_y[i]);
+            if (!(rx >= VS_EDGE && rx < p.width - VS_EDGE && ry >= VS_EDGE && ry < p.height - VS_EDGE)) continue;
+            kept.push_back({h_x[i], h_y[i], h_angle[i], l});
+            keep_idx.push_back(i);
+        }
+    for (int i = 0; i < n; ++i)
+        if (h_octave[i] < 0 || h_octave[i] >= p.n_levels) {
+            vs_set_error("vslam_orb_compute_host: keypoint octave %d outside the %d planned levels", h_octave[i], p.n_levels);
+            return VSLAM_E_INVALID;
+        }
+    const int m = (int)kept.size();
+    if (m == 0) return VSLAM_OK;
+    int rc = vs_ensure_host_staging(o);
+    if (rc) return rc;
+    cudaStream_t s = o->stream;
+    VS_CUDA(cudaMemcpyAsync(o->d_frames, h_frame, (size_t)p.width * p.height, cudaMemcpyHostToDevice, s));
+    o->last_stream = s; o->last_frames = o->d_frames; o->last_pitch = p.width; o->last_batch = 1;
+    o->prof_count = 0;
+    rc = vs_launch_levels(o, o->d_frames, 1, p.width, s);
+    if (rc) return rc;
+    VsGivenKp* d_k = nullptr;
+    uint8_t* d_d = nullptr;
+    VS_CUDA(cudaMalloc(&d_k, (size_t)m * sizeof(VsGivenKp)));
+    cudaError_t e = cudaMalloc(&d_d, (size_t)m * 32);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_k, kept.data(), (size_t)m * sizeof(VsGivenKp), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) {
+        ++g_vs_launches;
+        vs_describe_given_kernel<<<(m + 7) / 8, 256, 0, s>>>(p, o->d_frames, p.width, o->d_pyr, d_k, m, d_d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_desc, d_d, (size_t)m * 32, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_k);
+    if (d_d) cudaFree(d_d);
+    if (e != cudaSuccess) return vs_cuda_fail(e, "orb_compute", __FILE__, __LINE__);
+    memcpy(h_keep_index, keep_idx.data(), (size_t)m * sizeof(int32_t));
+    *n_out = m;
+    return VSLAM_OK;
+}
