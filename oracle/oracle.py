@@ -250,3 +250,25 @@ def match(d1, d2, ratio=0.75, ratio_test=True):
     idx, dist = bf_knn2(np.uint8(d1), np.uint8(d2))
     keep = ratio_filter(idx, dist, ratio, ratio_test)
     return [(int(i), int(idx[i, 0]), float(dist[i, 0])) for i in np.nonzero(keep)[0]]
+
+
+# ------------------------------------------------------------- distribute_keypoints
+def min_eigen_map(img):
+    """cv2.cornerMinEigenVal(img, 3, ksize=3) (inside goodFeaturesToTrack, extractor.py:123-129)."""
+    img = _u8(img)
+    h, w = img.shape
+    out = np.zeros((h, w), np.float32)
+    lib().orc_min_eigen_map(img.ctypes.data_as(C.c_void_p), w, h, out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def gftt_grid(img, n_features=2000, rows=8, cols=8, quality=0.01, min_distance=10.0):
+    """extractor.py:85-136: corner positions of distribute_keypoints -> (xy float32 [n,2], cell_count)."""
+    img = _u8(img)
+    h, w = img.shape
+    per = n_features // (rows * cols)
+    xy = np.zeros((max(rows * cols * per, 1), 2), np.float32)
+    cc = np.zeros(rows * cols, np.int32)
+    n = lib().orc_gftt_grid(img.ctypes.data_as(C.c_void_p), h, w, rows, cols, per, C.c_double(quality),
+                            C.c_double(min_distance), xy.ctypes.data_as(C.c_void_p), cc.ctypes.data_as(C.c_void_p))
+    return xy[:n].copy(), cc

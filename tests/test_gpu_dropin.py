@@ -1,0 +1,176 @@
+"""GPU tests of the drop-in classes (same names / signatures / return types as the reference's
+src/orbslam2 modules) against golden vectors produced by the reference's own classes."""
+import numpy as np
+import pytest
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+cv2 = pytest.importorskip("cv2")
+
+K_GERARD = np.array([796.7, 0.0, 239.0, 0.0, 787.8, 425.0, 0.0, 0.0, 1.0]).reshape(3, 3)
+
+
+def _kp_set(kps, desc):
+    return {(k.octave, k.pt[0], k.pt[1]): (k.angle, k.response, k.size, bytes(d)) for k, d in zip(kps, desc)}
+
+
+def _golden_set(g, tag, which):
+    pre = "%s_kp%d_" % (tag, which)
+    return {(int(o), float(x), float(y)): (float(a), float(r), float(s), bytes(d))
+            for x, y, o, a, r, s, d in zip(g[pre + "x"], g[pre + "y"], g[pre + "octave"], g[pre + "angle"],
+                                           g[pre + "response"], g[pre + "size"], g["%s_desc%d" % (tag, which)])}
+
+
+def test_detect_and_compute_equals_reference(synth640):
+    from orbslam2.extractor import ORBExtractor
+    g = load_golden("synth640.npz")
+    ex = ORBExtractor(n_features=2000)
+    assert (ex.n_features, ex.scale_factor, ex.n_levels, ex.ini_threshold, ex.min_threshold) == (2000, 1.2, 8, 20, 7)
+    kps, desc = ex.detect_and_compute(synth640.frame(0))
+    assert isinstance(kps, tuple) and isinstance(kps[0], cv2.KeyPoint) and kps[0].class_id == -1
+    assert desc.dtype == np.uint8 and desc.shape == (len(kps), 32) and desc.flags["C_CONTIGUOUS"]
+    assert _kp_set(kps, desc) == _golden_set(g, "s640", 1)          # 100 % of keypoints, bit-equal fields
+    assert [k.octave for k in kps] == sorted(k.octave for k in kps)  # level-major like cv2
+    # blank image -> ((), None), and then match() -> []
+    kps0, desc0 = ex.detect_and_compute(np.full((480, 640), 90, np.uint8))
+    assert kps0 == () and desc0 is None
+    from orbslam2.matcher import DescriptorMatcher
+    assert DescriptorMatcher().match(desc0, desc) == []
+
+
+@pytest.mark.parametrize("pair", ["pair01", "pair12"])
+def test_real_bgr_images_and_match_lists(pair):
+    from orbslam2.extractor import ORBExtractor
+    from orbslam2.matcher import DescriptorMatcher
+    g = load_golden(pair + ".npz")
+    ex = ORBExtractor()
+    # K0: BGR input goes through the gray conversion kernel
+    crop = ex._gray(g["bgr_crop"])
+    assert np.array_equal(crop, g["gray_crop"])
+    k1, d1 = ex.detect_and_compute(g["gray1"])
+    k2, d2 = ex.detect_and_compute(g["gray2"])
+    assert _kp_set(k1, d1) == _golden_set(g, pair, 1)
+    assert _kp_set(k2, d2) == _golden_set(g, pair, 2)
+    # matching is checked on the reference's descriptor arrays (its in-level keypoint order differs)
+    r1, r2 = g[pair + "_desc1"], g[pair + "_desc2"]
+    for r in (75, 80, 85):
+        ms = DescriptorMatcher(ratio_threshold=r / 100.0).match(r1, r2)
+        assert isinstance(ms[0], cv2.DMatch) and ms[0].imgIdx == 0
+        got = np.array([(m.queryIdx, m.trainIdx, m.distance) for m in ms], np.float64)
+        assert np.array_equal(got, g["%s_match_%d" % (pair, r)])
+    ms = DescriptorMatcher().match(r1, r2, ratio_test=False)
+    got = np.array([(m.queryIdx, m.trainIdx, m.distance) for m in ms], np.float64)
+    assert np.array_equal(got, g[pair + "_match_noratio"])
+    # non-uint8 descriptors are cast like the reference does
+    ms2 = DescriptorMatcher().match(r1.astype(np.int32), r2.astype(np.float32), ratio_test=False)
+    assert len(ms2) == len(ms)
+
+
+def test_gt_matcher_procedure_and_compute():
+    """src/tests/gt_test_matcher.py on the committed pairs: compute() at hand-labelled keypoints
+    then match(0.85) -> the reference's exact match list."""
+    from orbslam2.extractor import ORBExtractor
+    from orbslam2.matcher import DescriptorMatcher
+    gt = load_golden("gt_pairs.npz")
+    ex, m = ORBExtractor(), DescriptorMatcher(ratio_threshold=0.85)
+    for pair in ("pair01", "pair12"):
+        g = load_golden(pair + ".npz")
+        descs = []
+        for which in (1, 2):
+            pts = gt["%s_pts%d" % (pair, which)]
+            kps = [cv2.KeyPoint(float(x), float(y), 31) for x, y in pts]
+            out_kps, d = ex.compute(g["gray%d" % which], kps)
+            assert out_kps is kps                                  # the reference returns the caller's list
+            assert np.array_equal(d, gt["%s_desc%d" % (pair, which)])
+            descs.append(d)
+        ms = m.match(descs[0], descs[1])
+        got = np.array([(x.queryIdx, x.trainIdx, x.distance) for x in ms], np.float64)
+        assert np.array_equal(got, gt[pair + "_match85"])
+    # the matcher alone on all 20 pairs (descriptors from the reference)
+    for i in range(1, 21):
+        p = "pair%02d" % i
+        ms = m.match(gt[p + "_desc1"], gt[p + "_desc2"])
+        got = np.array([(x.queryIdx, x.trainIdx, x.distance) for x in ms], np.float64).reshape(-1, 3)
+        assert np.array_equal(got, gt[p + "_match85"])
+
+
+def test_compute_border_and_octaves(oracle, synth640):
+    from orbslam2.extractor import ORBExtractor
+    frame = synth640.frame(2)
+    rng = np.random.default_rng(3)
+    kps = [cv2.KeyPoint(float(rng.uniform(0, 640)), float(rng.uniform(0, 480)), 31, float(rng.uniform(-1, 360)), 0,
+                        int(rng.integers(0, 4))) for _ in range(300)]
+    ex = ORBExtractor()
+    out, d = ex.compute(frame, kps)
+    ref, keep = oracle.orb_compute(frame, [k.pt[0] for k in kps], [k.pt[1] for k in kps], [k.angle for k in kps],
+                                   [k.octave for k in kps])
+    assert out is kps and len(d) == len(ref) < len(kps)
+    assert np.array_equal(d, ref)
+    al_kps, al_d = ex.compute(frame, kps, aligned=True)
+    assert [kps[i] for i in keep] == al_kps and np.array_equal(al_d, ref)
+
+
+@pytest.mark.parametrize("name,tag", [("synth640.npz", "s640"), ("pair01.npz", "pair01")])
+def test_distribute_keypoints_equals_reference(name, tag, synth640):
+    from orbslam2.extractor import ORBExtractor
+    g = load_golden(name)
+    img = synth640.frame(0) if tag == "s640" else g["gray1"]
+    kps, desc = ORBExtractor(n_features=2000).distribute_keypoints(img)
+    assert isinstance(kps, list)
+    xy = np.array([k.pt for k in kps], np.float32)
+    assert np.array_equal(xy, g[tag + "_dist_xy"])                   # same corners, same order
+    assert all(k.angle == -1 and k.octave == 0 and k.size == 31 for k in kps)
+    assert np.array_equal(desc, g[tag + "_dist_desc"])              # N_all keypoints, N_in-border rows
+    assert len(desc) < len(kps)
+    k2, d2 = ORBExtractor(n_features=2000).extract_features(img)     # distributed=True is the default
+    assert len(k2) == len(kps) and np.array_equal(d2, desc)
+
+
+def test_match_with_mask(oracle):
+    from orbslam2.matcher import DescriptorMatcher
+    rng = np.random.default_rng(5)
+    d1 = rng.integers(0, 256, (40, 32), dtype=np.uint8)
+    d2 = rng.integers(0, 256, (300, 32), dtype=np.uint8)
+    mask = (rng.random((40, 300)) < 0.2).astype(np.uint8)
+    mask[7] = 0
+    ms = DescriptorMatcher().match_with_mask(d1, d2, mask)
+    idx, dist = oracle.bf_match_masked(d1, d2, mask)
+    exp = sorted([(float(dist[q]), q, int(idx[q])) for q in range(40) if idx[q] >= 0], key=lambda t: t[0])
+    assert [(m.distance, m.queryIdx, m.trainIdx) for m in ms] == exp
+
+
+def test_filter_by_fundamental_and_initializer():
+    from orbslam2.extractor import ORBExtractor
+    from orbslam2.initializer import MapInitializer
+    from orbslam2.matcher import DescriptorMatcher
+    g = load_golden("pair01.npz")
+    ex, m = ORBExtractor(), DescriptorMatcher()
+    k1, d1 = ex.detect_and_compute(g["gray1"])
+    k2, d2 = ex.detect_and_compute(g["gray2"])
+    matches = m.match(d1, d2)
+    assert abs(len(matches) - len(g["pair01_match_75"])) <= 2      # same set up to in-level order ties
+    filt, mask = m.filter_matches_by_fundamental(k1, k2, matches, 3.0)
+    assert mask.dtype == bool and len(mask) == len(matches) and len(filt) == int(mask.sum())
+    assert int(mask.sum()) >= 0.97 * int(g["pair01_Fmask"].sum())
+    init = MapInitializer(K_GERARD, min_matches=50, min_inliers_ratio=0.8)
+    assert init.initialize(k2, d2, m, g["gray2"]) == (False, None, None, None, None)
+    init.set_first_frame(k1, d1, g["gray1"])
+    ok, R, t, pts, vm = init.initialize(k2, d2, m, g["gray2"])
+    assert ok is True and R.shape == (3, 3) and t.shape == (3, 1) and init.initialization_done
+    assert len(pts) >= 20 and len(pts) == len(vm)
+    assert set(pts[0]) == {"position", "color", "keypoint_references", "observed_frames"}
+    assert pts[0]["position"].dtype == np.float32 and pts[0]["position"].shape == (3,)
+    # agreement with the reference's initialisation (its own RANSAC stream): same pose, similar map
+    Rr, tr = g["pair01_init_R"], g["pair01_init_t"]
+    ang = np.degrees(np.arccos(np.clip((np.trace(R @ Rr.T) - 1) / 2, -1, 1)))
+    assert ang < 0.5, ang
+    # the translation direction is weakly constrained on this pair (two RANSAC streams at a 3 px
+    # threshold differ by ~14 degrees in cv2 itself across seeds); require the same hemisphere cone
+    assert float(np.dot(t.ravel(), tr.ravel())) > 0.9
+    # the map size depends on recoverPose's depth < 50 baselines gate, hence on the E the RANSAC
+    # stream happened to pick (reference: 213 points); the reference's own test asserts >= 20
+    # (src/tests/test_map_initializer.py:106-107)
+    assert len(pts) >= 20
+    vis = init.draw_initialization(g["gray1"], g["gray2"], vm[:50])
+    assert isinstance(vis, np.ndarray) and vis.size > 0

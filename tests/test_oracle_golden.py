@@ -1,0 +1,126 @@
+"""CPU tests: the oracle against golden vectors produced by RUNNING THE REFERENCE
+(tests/golden/make_golden.py), so that the oracle the GPU tests check against is pinned."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, load_golden
+
+K_GERARD = np.array([796.7, 0.0, 239.0, 0.0, 787.8, 425.0, 0.0, 0.0, 1.0]).reshape(3, 3)
+K_SYNTH = np.array([[320.0, 0, 320], [0, 320, 240], [0, 0, 1]])
+
+
+def _kp_set(x, y, octave, angle, response, desc):
+    return {(int(o), float(a), float(b)): (float(c), float(d), bytes(e))
+            for a, b, o, c, d, e in zip(x, y, octave, angle, response, desc)}
+
+
+def _check_extract(O, gray, g, tag, which):
+    r = O.orb_detect_and_compute(gray, 2000)
+    pre = "%s_kp%d_" % (tag, which)
+    ref = _kp_set(g[pre + "x"], g[pre + "y"], g[pre + "octave"], g[pre + "angle"], g[pre + "response"],
+                  g["%s_desc%d" % (tag, which)])
+    got = _kp_set(r["x"], r["y"], r["octave"], r["angle"], r["response"], r["desc"])
+    assert len(got) == len(r["x"]) and len(ref) == len(g[pre + "x"])
+    assert got == ref                                  # same keypoints, bit-equal angle/response, same descriptors
+    assert np.allclose(r["size"], 31.0 * np.float32(1.2) ** r["octave"], rtol=1e-6)
+
+
+def test_pattern_hash():
+    rows = []
+    for line in open(os.path.join(ROOT, "oracle", "rbrief_pattern.inc")):
+        if line.startswith("{"):
+            rows.append([int(v) for v in line.strip().strip("{},").split(",")])
+    pat = np.array(rows, "<i4")
+    assert pat.shape == (256, 4)
+    assert hashlib.sha256(pat.tobytes()).hexdigest() == "7e645581387b82784797e8adddb9b6f0c12611859fda09ca8a9bec96d767a05f"
+    prod = open(os.path.join(ROOT, "visual-slam_b200", "csrc", "rbrief_pattern.inc")).read()
+    assert prod == open(os.path.join(ROOT, "oracle", "rbrief_pattern.inc")).read()
+
+
+def test_synthetic_generator_is_stable(synth640):
+    g = load_golden("synth640.npz")
+    sha = hashlib.sha256(synth640.frame(0).tobytes()).digest()
+    assert bytes(g["frame0_sha"]) == sha
+
+
+def test_extract_synthetic_matches_reference(oracle, synth640):
+    g = load_golden("synth640.npz")
+    _check_extract(oracle, synth640.frame(0), g, "s640", 1)
+    _check_extract(oracle, synth640.frame(1), g, "s640", 2)
+
+
+@pytest.mark.parametrize("pair", ["pair01", "pair12"])
+def test_extract_real_images_match_reference(oracle, pair):
+    g = load_golden(pair + ".npz")
+    assert np.array_equal(oracle.bgr2gray(g["bgr_crop"]), g["gray_crop"])
+    _check_extract(oracle, g["gray1"], g, pair, 1)
+    _check_extract(oracle, g["gray2"], g, pair, 2)
+
+
+@pytest.mark.parametrize("name,tag", [("synth640.npz", "s640"), ("pair01.npz", "pair01"), ("pair12.npz", "pair12")])
+def test_match_lists_equal_reference(oracle, name, tag):
+    g = load_golden(name)
+    d1, d2 = g[tag + "_desc1"], g[tag + "_desc2"]
+    for r in (75, 80, 85):
+        got = np.array(oracle.match(d1, d2, r / 100.0), np.float64).reshape(-1, 3)
+        assert np.array_equal(got, g["%s_match_%d" % (tag, r)])
+    got = np.array(oracle.match(d1, d2, 0.75, ratio_test=False), np.float64).reshape(-1, 3)
+    assert np.array_equal(got, g[tag + "_match_noratio"])
+
+
+def test_gt_matcher_table(oracle):
+    """src/tests/gt_test_matcher.py:59-132 on all 20 fixture pairs: identical match lists and
+    the precision / recall table of BASELINE.md section 2."""
+    g = load_golden("gt_pairs.npz")
+    prec, rec = [], []
+    for i in range(1, 21):
+        p = "pair%02d" % i
+        ms = oracle.match(g[p + "_desc1"], g[p + "_desc2"], 0.85)
+        assert np.array_equal(np.array(ms, np.float64).reshape(-1, 3), g[p + "_match85"])
+        pred = {(a, b) for a, b, _ in ms}
+        gts = {tuple(x) for x in g[p + "_gt"].tolist()}
+        tp = len(pred & gts)
+        prec.append(tp / len(pred))
+        rec.append(tp / len(gts))
+    assert np.allclose(prec, g["precision"]) and np.allclose(rec, g["recall"])
+    assert round(float(np.mean(prec)), 3) == 0.902 and round(float(np.mean(rec)), 3) == 0.908
+    table = [(0.92, 0.88), (0.94, 0.91), (0.93, 0.84), (0.93, 0.96), (0.97, 1.00), (0.83, 0.94), (0.95, 0.90),
+             (0.97, 0.88), (0.94, 1.00), (0.96, 0.87), (0.94, 0.94), (0.68, 0.94), (0.85, 0.77), (1.00, 0.93),
+             (0.76, 0.93), (1.00, 0.88), (0.86, 0.89), (0.93, 1.00), (0.89, 0.89), (0.77, 0.80)]
+    assert [(round(a, 2), round(b, 2)) for a, b in zip(prec, rec)] == table
+
+
+@pytest.mark.parametrize("pair", ["pair01", "pair12"])
+def test_compute_at_gt_keypoints(oracle, pair):
+    g, gt = load_golden(pair + ".npz"), load_golden("gt_pairs.npz")
+    for which in (1, 2):
+        pts = gt["%s_pts%d" % (pair, which)]
+        desc, keep = oracle.orb_compute(g["gray%d" % which], pts[:, 0], pts[:, 1], np.full(len(pts), -1.0), np.zeros(len(pts)))
+        assert np.array_equal(desc, gt["%s_desc%d" % (pair, which)])
+        assert np.array_equal(keep, np.arange(len(keep)))
+
+
+@pytest.mark.parametrize("name,tag,K", [("synth640.npz", "s640", K_SYNTH), ("pair01.npz", "pair01", K_GERARD),
+                                        ("pair12.npz", "pair12", K_GERARD)])
+def test_geometry_scoring_and_pose(name, tag, K):
+    from oracle import geom_oracle as G
+    g = load_golden(name)
+    p1, p2 = g[tag + "_p1"], g[tag + "_p2"]
+    # the masks cv2 reports are exactly its error function applied to the model it returns
+    assert np.array_equal(G.score_fundamental(g[tag + "_F"], p1, p2, 3.0), g[tag + "_Fmask"])
+    for thr in (1, 3):
+        E, emask = g["%s_E_%d" % (tag, thr)], g["%s_Emask_%d" % (tag, thr)]
+        assert np.array_equal(G.score_essential(E, p1, p2, K, float(thr)), emask)
+        n, R, t, m = G.recover_pose(E, p1, p2, K, emask)
+        assert n == int(g["%s_pose_n_%d" % (tag, thr)])
+        assert np.array_equal(m != 0, g["%s_pose_mask_%d" % (tag, thr)] != 0)
+        assert np.allclose(R, g["%s_pose_R_%d" % (tag, thr)], atol=1e-9)
+        assert np.allclose(t, g["%s_pose_t_%d" % (tag, thr)], atol=1e-9)
+    sel = g[tag + "_pose_mask_3"] != 0
+    X = G.triangulate(g[tag + "_tri_P1"], g[tag + "_tri_P2"], p1[sel], p2[sel])
+    ref = g[tag + "_tri_X"]
+    assert X.shape == ref.shape
+    assert np.allclose(X[:3] / X[3], ref[:3] / ref[3], rtol=2e-3, atol=1e-4)   # float32 output of a 4x4 SVD
