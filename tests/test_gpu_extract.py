@@ -66,7 +66,9 @@ def test_detect_and_compute_synthetic_640(oracle, synth640):
         _compare_extract(oracle, frames[f], kp[f], desc[f], int(cnt[f]))
     # batch independence: a single-frame call gives the same rows
     kp1, desc1, cnt1 = h.detect_and_compute_host(frames[1])
-    assert cnt1[0] == cnt[1] and np.array_equal(desc1[0], desc[1]) and np.array_equal(kp1[0], kp[1])
+    n = int(cnt[1])
+    assert cnt1[0] == cnt[1] and np.array_equal(desc1[0][:n], desc[1][:n])
+    assert kp1[0][:n].tobytes() == kp[1][:n].tobytes()
     h.close()
 
 

@@ -118,6 +118,33 @@ static int build_plan(const vslam_orb_params& prm, VsPlan& p, std::vector<uint32
             linear_exact_table(p.lv[l - 1].h, L.h, tab.data() + L.taby_off);
         }
     }
+    // extent of the parent region one tile of the level kernel stages in shared memory
+    // (same arithmetic as the kernel: reflected tile coordinates -> table entries -> bounding box)
+    p.par_w = 4; p.par_h = 1;
+    for (int l = 1; l < prm.n_levels; ++l) {
+        const VsLevel& L = p.lv[l];
+        if (L.w <= 0 || L.h <= 0) continue;
+        for (int axis = 0; axis < 2; ++axis) {
+            const int n = axis == 0 ? L.w : L.h, src_n = axis == 0 ? p.lv[l - 1].w : p.lv[l - 1].h;
+            const int tile = axis == 0 ? VS_TW : VS_TH, tiles = axis == 0 ? L.tiles_x : L.tiles_y;
+            const uint32_t* t = tab.data() + (axis == 0 ? L.tabx_off : L.taby_off);
+            for (int k = 0; k < tiles; ++k) {
+                int lo = 0x7fffffff, hi = 0;
+                for (int c = 0; c < tile + 2 * VS_HALO; ++c) {
+                    int i0 = (int)(t[vs_reflect101(k * tile - VS_HALO + c, n)] & 0xffff);
+                    lo = i0 < lo ? i0 : lo;
+                    hi = i0 > hi ? i0 : hi;
+                }
+                hi = hi + 1 < src_n - 1 ? hi + 1 : src_n - 1;
+                if (axis == 0) {
+                    int wbytes = ((hi - (lo & ~3)) / 4 + 1) * 4;
+                    p.par_w = wbytes > p.par_w ? wbytes : p.par_w;
+                } else {
+                    p.par_h = hi - lo + 1 > p.par_h ? hi - lo + 1 : p.par_h;
+                }
+            }
+        }
+    }
     p.pyr_frame_bytes = align_up(pyr, 256);
     p.cand_frame_entries = align_up(cand, 32);
     p.stage_frame_entries = stage;
@@ -156,6 +183,8 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
         return VSLAM_E_INVALID;
     }
     vs_configure_select_smem(max_stage * 8);
+    rc = vs_configure_level_smem(o->plan);
+    if (rc) { delete o; return rc; }
     cudaGetDevice(&o->device);
 #define ALLOC(ptr, bytes)                                                   \
     do {                                                                    \
@@ -250,6 +279,10 @@ int vs_ensure_host_staging(vslam_orb* o)
     VS_CUDA(cudaMalloc((void**)&o->d_count, B * sizeof(int32_t)));
     VS_CUDA(cudaMalloc((void**)&o->d_match, B * (size_t)p.kp_cap * 3 * sizeof(int32_t)));
     VS_CUDA(cudaMalloc((void**)&o->d_match_count, B * sizeof(int32_t)));
+    // rows past a frame's count are never written by the kernels: make them read as zeros
+    VS_CUDA(cudaMemset(o->d_kp, 0, B * p.kp_cap * sizeof(vslam_keypoint)));
+    VS_CUDA(cudaMemset(o->d_desc, 0, B * (size_t)p.kp_cap * 32));
+    VS_CUDA(cudaMemset(o->d_match, 0, B * (size_t)p.kp_cap * 3 * sizeof(int32_t)));
     return VSLAM_OK;
 }
 

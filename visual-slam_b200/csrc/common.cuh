@@ -12,9 +12,10 @@
 #define VS_HALF_PATCH 15  // patchSize 31, extractor.py:46
 
 // Fused level kernel tile: TW x TH output pixels, halo of 4 (3 for the FAST circle
-// and the 7-tap blur, +1 for the NMS neighbours' scores).
+// and the 7-tap blur, +1 for the NMS neighbours' scores).  TH = 30 makes the score rows
+// (TH + 2) x 16 four-pixel words exactly 2 items per thread of a 256-thread CTA.
 #define VS_TW 64
-#define VS_TH 32
+#define VS_TH 30
 #define VS_HALO 4
 
 extern unsigned long long g_vs_launches;   // kernels launched by this library (bench.py reports it)
@@ -63,6 +64,7 @@ struct VsPlan {
     size_t pyr_frame_bytes;     // bytes of one frame's pyramid block (raw 1.. + blur 0..)
     size_t cand_frame_entries;
     size_t stage_frame_entries;
+    int par_w, par_h;           // level kernel: shared-memory extent of the staged parent region
 };
 
 // profiling slots: 0..15 level kernels, then the per-keypoint kernels and matching
@@ -115,6 +117,7 @@ struct vslam_orb {
 #define VS_CTR_STRIDE (4 + 256)
 
 // kernels / launchers implemented in the other translation units
+int vs_configure_level_smem(const VsPlan& p);
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
