@@ -105,15 +105,81 @@ __device__ __forceinline__ float lane_hi_f(uint32_t w)
     return __fadd_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)), -8388608.0f);
 }
 
-// four source bytes at column gx of a row (reflecting / byte-wise when the word is not
-// wholly inside the row or the row is not 4-byte aligned)
-__device__ __forceinline__ uint32_t load4_reflect(const uint8_t* row, int gx, int W, bool aligned)
+// four source bytes at column gx of a row, byte-wise with REFLECT_101 (words that are not
+// wholly inside the row, or rows that are not 4-byte aligned)
+__device__ __noinline__ uint32_t load4_reflect(const uint8_t* row, int gx, int W)
 {
-    if (aligned && gx >= 0 && gx + 3 < W) return __ldg((const uint32_t*)(row + gx));
     uint32_t u = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) u |= (uint32_t)__ldg(row + vs_reflect101(gx + j, W)) << (8 * j);
     return u;
+}
+
+// Row pass of the 7-tap Gaussian for 8 adjacent pixels: q = 8 words of the 16-bit tile starting 4
+// columns left of the first pixel, dst = 8 floats.  cv2 order: k0*x0, then one tap at a time.
+template <bool FMA>
+__device__ __forceinline__ void blur_row_item(const uint2* q, float* dst)
+{
+    const float k0 = __uint_as_float(c_gauss_bits[0]), k1 = __uint_as_float(c_gauss_bits[1]),
+                k2 = __uint_as_float(c_gauss_bits[2]), k3 = __uint_as_float(c_gauss_bits[3]);
+    const uint2 a = q[0], b = q[1], c = q[2], d = q[3];
+    float x[14];                                                      // tile columns +1 .. +14
+    x[0] = lane_hi_f(a.x); x[1] = lane_lo_f(a.y); x[2] = lane_hi_f(a.y);
+    x[3] = lane_lo_f(b.x); x[4] = lane_hi_f(b.x); x[5] = lane_lo_f(b.y); x[6] = lane_hi_f(b.y);
+    x[7] = lane_lo_f(c.x); x[8] = lane_hi_f(c.x); x[9] = lane_lo_f(c.y); x[10] = lane_hi_f(c.y);
+    x[11] = lane_lo_f(d.x); x[12] = lane_hi_f(d.x); x[13] = lane_lo_f(d.y);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float s = __fmul_rn(k0, x[j]);
+        if (FMA) {
+            s = __fmaf_rn(k1, x[j + 1], s); s = __fmaf_rn(k2, x[j + 2], s); s = __fmaf_rn(k3, x[j + 3], s);
+            s = __fmaf_rn(k2, x[j + 4], s); s = __fmaf_rn(k1, x[j + 5], s); s = __fmaf_rn(k0, x[j + 6], s);
+        } else {
+            s = __fadd_rn(s, __fmul_rn(k1, x[j + 1])); s = __fadd_rn(s, __fmul_rn(k2, x[j + 2]));
+            s = __fadd_rn(s, __fmul_rn(k3, x[j + 3])); s = __fadd_rn(s, __fmul_rn(k2, x[j + 4]));
+            s = __fadd_rn(s, __fmul_rn(k1, x[j + 5])); s = __fadd_rn(s, __fmul_rn(k0, x[j + 6]));
+        }
+        o[j] = s;
+    }
+    *(float4*)dst = make_float4(o[0], o[1], o[2], o[3]);
+    *(float4*)(dst + 4) = make_float4(o[4], o[5], o[6], o[7]);
+}
+
+// Column pass for 4 columns x 2 output rows: p = row-pass results of the first output row's
+// top tap (8 rows of VS_TW floats are read).  cv2 order: k3*c, then symmetric pairs inner..outer;
+// the result is rounded half-to-even to a byte (0 <= s < 255.5) in the mantissa of 1.5*2^23 + s.
+template <bool FMA>
+__device__ __forceinline__ void blur_col_item(const float* p, uint32_t& out0, uint32_t& out1)
+{
+    const float k0 = __uint_as_float(c_gauss_bits[0]), k1 = __uint_as_float(c_gauss_bits[1]),
+                k2 = __uint_as_float(c_gauss_bits[2]), k3 = __uint_as_float(c_gauss_bits[3]);
+    float r[8][4];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float4 v = *(const float4*)(p + k * VS_TW);
+        r[k][0] = v.x; r[k][1] = v.y; r[k][2] = v.z; r[k][3] = v.w;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t u[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float s = __fmul_rn(k3, r[h + 3][j]);
+            const float p1 = __fadd_rn(r[h + 2][j], r[h + 4][j]);
+            const float p2 = __fadd_rn(r[h + 1][j], r[h + 5][j]);
+            const float p3 = __fadd_rn(r[h + 0][j], r[h + 6][j]);
+            if (FMA) {
+                s = __fmaf_rn(k2, p1, s); s = __fmaf_rn(k1, p2, s); s = __fmaf_rn(k0, p3, s);
+            } else {
+                s = __fadd_rn(s, __fmul_rn(k2, p1)); s = __fadd_rn(s, __fmul_rn(k1, p2));
+                s = __fadd_rn(s, __fmul_rn(k0, p3));
+            }
+            u[j] = __float_as_uint(__fadd_rn(s, 12582912.0f));
+        }
+        const uint32_t packed = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
+        if (h == 0) out0 = packed; else out1 = packed;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -123,7 +189,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 int32_t* __restrict__ counters)
 {
     __shared__ __align__(16) uint16_t s_raw[RAW_H * RAW_S];
-    __shared__ __align__(16) uint8_t s_sc[SC_H * SC_S];
+    __shared__ __align__(16) uint16_t s_sc[SC_H * SC_S];   // max(S - thr, 0), 16-bit lanes
     __shared__ __align__(16) float s_row[BL_ROWS * VS_TW];
     __shared__ uint32_t s_hist[256];
     __shared__ VsCand s_list[LIST_CAP];
@@ -146,12 +212,26 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     if (level == 0) {
         const uint8_t* src = frames + (size_t)b * fstride;
         const bool aligned = (((size_t)src | (size_t)fpitch) & 3) == 0;
-        for (int i = tid; i < RAW_H * (RAW_W / 4); i += 256) {
-            int r = i / (RAW_W / 4), wd = i - r * (RAW_W / 4);
-            int gy = vs_reflect101(y0 - VS_HALO + r, H);
-            uint32_t u = load4_reflect(src + (size_t)gy * fpitch, x0 - VS_HALO + 4 * wd, W, aligned);
-            uint2 o = make_uint2(__byte_perm(u, 0, 0x4140), __byte_perm(u, 0, 0x4342));
-            *(uint2*)(s_raw + r * RAW_S + 4 * wd) = o;
+        // thread = one 4-pixel word column x up to 3 rows; the loads are issued before any store
+        const int wd = tid % (RAW_W / 4), rg = tid / (RAW_W / 4);        // 18 word columns x 14 row groups
+        if (rg < 14) {
+            const int gx = x0 - VS_HALO + 4 * wd;
+            const bool fast = aligned && gx >= 0 && gx + 3 < W;
+            uint32_t u[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int r = rg + 14 * k;
+                if (r < RAW_H) {
+                    const uint8_t* row = src + (size_t)vs_reflect101(y0 - VS_HALO + r, H) * fpitch;
+                    u[k] = fast ? __ldg((const uint32_t*)(row + gx)) : load4_reflect(row, gx, W);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int r = rg + 14 * k;
+                if (r < RAW_H)
+                    *(uint2*)(s_raw + r * RAW_S + 4 * wd) = make_uint2(__byte_perm(u[k], 0, 0x4140), __byte_perm(u[k], 0, 0x4342));
+            }
         }
     } else {
         const VsLevel& P = plan.lv[level - 1];
@@ -184,36 +264,65 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         __syncthreads();
         const int pxa = s_bnd[0] & ~3, py0 = s_bnd[2];
         const int nwords = (s_bnd[1] - pxa) / 4 + 1, nrows = s_bnd[3] - py0 + 1;
-        for (int i = tid; i < nrows * nwords; i += 256) {
-            int r = i / nwords, wd = i - r * nwords;
-            const uint8_t* row = src + (size_t)(py0 + r) * sp;
-            int gx = pxa + 4 * wd;
-            uint32_t u;
-            if (aligned && gx + 3 < sw) u = __ldg((const uint32_t*)(row + gx));
-            else {
-                u = 0;
+        {   // stage the parent region: thread = one word column x every G-th row, 4 loads in flight
+            const int PWW = PW >> 2, G = 256 / PWW;
+            const int wd = tid % PWW, rg = tid / PWW;
+            if (rg < G && wd < nwords) {
+                const int gx = pxa + 4 * wd;
+                const bool fast = aligned && gx + 3 < sw;
+                for (int r0 = rg; r0 < nrows; r0 += 4 * G) {
+                    uint32_t u[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) u |= (uint32_t)__ldg(row + min(gx + j, sw - 1)) << (8 * j);
+                    for (int k = 0; k < 4; ++k) {
+                        const int r = r0 + k * G;
+                        if (r < nrows) {
+                            const uint8_t* row = src + (size_t)(py0 + r) * sp;
+                            if (fast) u[k] = __ldg((const uint32_t*)(row + gx));
+                            else {
+                                u[k] = 0;
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) u[k] |= (uint32_t)__ldg(row + min(gx + j, sw - 1)) << (8 * j);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int r = r0 + k * G;
+                        if (r < nrows) *(uint32_t*)(s_par + r * PW + 4 * wd) = u[k];
+                    }
+                }
             }
-            *(uint32_t*)(s_par + r * PW + 4 * wd) = u;
         }
         __syncthreads();
-        for (int i = tid; i < nrows * RAW_W; i += 256) {
-            int r = i / RAW_W, c = i - r * RAW_W;
-            uint32_t e = s_tx[c];
-            int i0 = (int)(e & 0xffff), a = (int)(e >> 16);
-            int i1 = min(i0 + 1, sw - 1);
-            const uint8_t* p = s_par + r * PW - pxa;
-            s_h[i] = (uint16_t)((uint32_t)p[i0] * (256 - a) + (uint32_t)p[i1] * a);
+        // separable INTER_LINEAR_EXACT: thread = one column pair x every 7th row, so that the table
+        // entries are loop invariant.  A column with i0 = sw-1 has weight 0 on its right neighbour,
+        // whatever that byte is.
+        const int cp = tid % (RAW_W / 2), rg7 = tid / (RAW_W / 2);       // 36 column pairs x 7 row groups
+        uint32_t* s_h32 = (uint32_t*)s_h;
+        if (rg7 < 7) {
+            const uint32_t ea = s_tx[2 * cp], eb = s_tx[2 * cp + 1];
+            const int ia = (int)(ea & 0xffff) - pxa, ib = (int)(eb & 0xffff) - pxa;
+            const uint32_t aa = ea >> 16, ab = eb >> 16;
+            for (int r = rg7; r < nrows; r += 7) {
+                const uint8_t* p = s_par + r * PW;
+                const uint32_t ha = (uint32_t)p[ia] * (256 - aa) + (uint32_t)p[ia + 1] * aa;
+                const uint32_t hb = (uint32_t)p[ib] * (256 - ab) + (uint32_t)p[ib + 1] * ab;
+                s_h32[r * (RAW_W / 2) + cp] = ha | (hb << 16);
+            }
         }
         __syncthreads();
-        for (int i = tid; i < RAW_H * RAW_W; i += 256) {
-            int r = i / RAW_W, c = i - r * RAW_W;
-            uint32_t e = s_ty[r];
-            int j0 = (int)(e & 0xffff), bq = (int)(e >> 16);
-            int j1 = min(j0 + 1, sh - 1);
-            uint32_t v = (uint32_t)s_h[(j0 - py0) * RAW_W + c] * (256 - bq) + (uint32_t)s_h[(j1 - py0) * RAW_W + c] * bq;
-            s_raw[r * RAW_S + c] = (uint16_t)((v + 32768u) >> 16);
+        if (rg7 < 7) {
+            uint32_t* s_raw32 = (uint32_t*)s_raw;
+            for (int r = rg7; r < RAW_H; r += 7) {
+                const uint32_t e = s_ty[r];
+                const int j0 = (int)(e & 0xffff);
+                const uint32_t bq = e >> 16;
+                const int j1 = min(j0 + 1, sh - 1);
+                const uint32_t h0 = s_h32[(j0 - py0) * (RAW_W / 2) + cp], h1 = s_h32[(j1 - py0) * (RAW_W / 2) + cp];
+                const uint32_t lo = (h0 & 0xffff) * (256 - bq) + (h1 & 0xffff) * bq + 32768u;
+                const uint32_t hi = (h0 >> 16) * (256 - bq) + (h1 >> 16) * bq + 32768u;
+                s_raw32[r * (RAW_S / 2) + cp] = (lo >> 16) | (hi & 0xffff0000u);
+            }
         }
     }
     __syncthreads();
@@ -240,7 +349,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     for (int i = tid; i < SC_H * (VS_TW / 4); i += 256) {
         const int w = i & 15, r = i >> 4;
         const int gy = y0 - 1 + r, gx = x0 + 4 * w;
-        uint32_t packed = 0;
+        uint32_t oA = 0, oB = 0;
         if (gy >= cy_lo && gy <= cy_hi && gx + 3 >= cx_lo && gx <= cx_hi) {
             const uint16_t* base = s_raw + (r + 3) * RAW_S + 4 * w;   // word 2 of this row = pixels 0,1
             uint32_t vA[16], vB[16], cA, cB;
@@ -285,15 +394,16 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 vA[12] = fsr16(a.x, a.y); vB[12] = fsr16(a.y, m.x);
                 cA = m.x; cB = m.y;
             }
-            const uint32_t oA = fast_pair(vA, cA, kbias), oB = fast_pair(vB, cB, kbias);
-            packed = __byte_perm(oA, oB, 0x6420);
+            oA = fast_pair(vA, cA, kbias);
+            oB = fast_pair(vB, cB, kbias);
             if (gx < cx_lo || gx + 3 > cx_hi) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (gx + j < cx_lo || gx + j > cx_hi) packed &= ~(0xffu << (8 * j));
+                if (gx + 0 < cx_lo || gx + 0 > cx_hi) oA &= 0xffff0000u;
+                if (gx + 1 < cx_lo || gx + 1 > cx_hi) oA &= 0x0000ffffu;
+                if (gx + 2 < cx_lo || gx + 2 > cx_hi) oB &= 0xffff0000u;
+                if (gx + 3 < cx_lo || gx + 3 > cx_hi) oB &= 0x0000ffffu;
             }
         }
-        *(uint32_t*)(s_sc + r * SC_S + 4 + 4 * w) = packed;
+        *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(oA, oB);
     }
     if (tid < 2 * SC_H) {   // ring columns tx = -1 and tx = TW
         const int r = tid % SC_H, side = tid / SC_H;
@@ -302,32 +412,39 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         int sc = 0;
         if (gy >= cy_lo && gy <= cy_hi && gx >= cx_lo && gx <= cx_hi)
             sc = fast_single(s_raw + (r + 3) * RAW_S + tx + VS_HALO, thr);
-        s_sc[r * SC_S + 4 + tx] = (uint8_t)sc;
+        s_sc[r * SC_S + 4 + tx] = (uint16_t)sc;
     }
     __syncthreads();
 
     // non-max suppression (strict >, non-corners count as 0) + 31-px border
     for (int i = tid; i < VS_TH * (VS_TW / 4); i += 256) {
         const int w = i & 15, ty = i >> 4;
-        const uint8_t* q = s_sc + (ty + 1) * SC_S + 4 + 4 * w;
-        const uint32_t C = *(const uint32_t*)q;
-        if (C == 0) continue;
+        // words of the score row around the 4 pixels: W1 = (tx-2, tx-1), W2 = (p0, p1), W3 = (p2, p3), W4 = (tx+4, tx+5)
+        const uint16_t* q = s_sc + (ty + 1) * SC_S + 4 * w;
+        const uint2 cm = *(const uint2*)(q + 4);
+        if ((cm.x | cm.y) == 0) continue;
         const int gy = y0 + ty;
         if (gy < VS_EDGE || gy >= H - VS_EDGE) continue;
-        const unsigned long long up = (unsigned long long)q[-SC_S - 1] | ((unsigned long long)*(const uint32_t*)(q - SC_S) << 8) |
-                                      ((unsigned long long)q[-SC_S + 4] << 40);
-        const unsigned long long mid = (unsigned long long)q[-1] | ((unsigned long long)C << 8) | ((unsigned long long)q[4] << 40);
-        const unsigned long long dn = (unsigned long long)q[SC_S - 1] | ((unsigned long long)*(const uint32_t*)(q + SC_S) << 8) |
-                                      ((unsigned long long)q[SC_S + 4] << 40);
+        const uint32_t m1 = *(const uint32_t*)(q + 2), m4 = *(const uint32_t*)(q + 8);
+        const uint2 cu = *(const uint2*)(q - SC_S + 4), cd = *(const uint2*)(q + SC_S + 4);
+        const uint32_t u1 = *(const uint32_t*)(q - SC_S + 2), u4 = *(const uint32_t*)(q - SC_S + 8);
+        const uint32_t d1 = *(const uint32_t*)(q + SC_S + 2), d4 = *(const uint32_t*)(q + SC_S + 8);
+        // per lane: max of the 8 neighbours; pair A = (p0, p1), pair B = (p2, p3)
+        const uint32_t um = fsr16(cu.x, cu.y), dm = fsr16(cd.x, cd.y), mm = fsr16(cm.x, cm.y);
+        const uint32_t nbA = __vimax3_u16x2(__vimax3_u16x2(fsr16(u1, cu.x), cu.x, um), __vimax3_u16x2(fsr16(d1, cd.x), cd.x, dm),
+                                            __vmaxu2(fsr16(m1, cm.x), mm));
+        const uint32_t nbB = __vimax3_u16x2(__vimax3_u16x2(um, cu.y, fsr16(cu.y, u4)), __vimax3_u16x2(dm, cd.y, fsr16(cd.y, d4)),
+                                            __vmaxu2(mm, fsr16(cm.y, m4)));
+        // bit 15 of a lane of (c + 0x7fff - nb) is set iff c > nb (no carry between lanes: both < 256)
+        const uint32_t kA = ((cm.x + 0x7fff7fffu) - nbA) & 0x80008000u, kB = ((cm.y + 0x7fff7fffu) - nbB) & 0x80008000u;
+        if ((kA | kB) == 0) continue;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const int v = (int)((C >> (8 * j)) & 0xff);
+            const uint32_t kk = j < 2 ? kA : kB, cc = j < 2 ? cm.x : cm.y;
             const int gx = x0 + 4 * w + j;
-            if (v == 0 || gx < VS_EDGE || gx >= W - VS_EDGE) continue;
-            const uint32_t u = (uint32_t)(up >> (8 * j)), m = (uint32_t)(mid >> (8 * j)), d = (uint32_t)(dn >> (8 * j));
-            const int nb = max(max(max((int)(u & 0xff), (int)((u >> 8) & 0xff)), max((int)((u >> 16) & 0xff), (int)(m & 0xff))),
-                               max(max((int)((m >> 16) & 0xff), (int)(d & 0xff)), max((int)((d >> 8) & 0xff), (int)((d >> 16) & 0xff))));
-            if (v > nb) {
+            if (!(kk & ((j & 1) ? 0x80000000u : 0x8000u)) || gx < VS_EDGE || gx >= W - VS_EDGE) continue;
+            const int v = (int)((j & 1) ? (cc >> 16) : (cc & 0xffff));
+            {
                 const int score = v + thr - 1;
                 int slot = atomicAdd(&s_n, 1);
                 VsCand c;
@@ -353,72 +470,28 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
 
     // ---- 4. Gaussian 7x7 (row pass, then column pass) -----------------------
     // cv2's vector blocks use FMA, its scalar tails do not: rows switch at W - W%32,
-    // columns at W - W%8; a 4-pixel group never straddles either boundary.
-    const float k0 = __uint_as_float(c_gauss_bits[0]), k1 = __uint_as_float(c_gauss_bits[1]),
-                k2 = __uint_as_float(c_gauss_bits[2]), k3 = __uint_as_float(c_gauss_bits[3]);
+    // columns at W - W%8; an aligned 8-pixel group never straddles either boundary.
     const int wrow = W & ~31, wcol = W & ~7;
-    for (int i = tid; i < BL_ROWS * (VS_TW / 4); i += 256) {
-        const int w = i & 15, rr = i >> 4;                            // s_row row rr <-> gy = y0 - 3 + rr
-        const uint2* q = (const uint2*)(s_raw + (rr + 1) * RAW_S + 4 * w);
-        const uint2 a = q[0], m = q[1], e = q[2];
-        float x[10];                                                  // columns 4w+1 .. 4w+10 of the tile
-        x[0] = lane_hi_f(a.x); x[1] = lane_lo_f(a.y); x[2] = lane_hi_f(a.y);
-        x[3] = lane_lo_f(m.x); x[4] = lane_hi_f(m.x); x[5] = lane_lo_f(m.y); x[6] = lane_hi_f(m.y);
-        x[7] = lane_lo_f(e.x); x[8] = lane_hi_f(e.x); x[9] = lane_lo_f(e.y);
-        float o[4];
-        if (x0 + 4 * w < wrow) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float s = __fmul_rn(k0, x[j]);
-                s = __fmaf_rn(k1, x[j + 1], s); s = __fmaf_rn(k2, x[j + 2], s); s = __fmaf_rn(k3, x[j + 3], s);
-                s = __fmaf_rn(k2, x[j + 4], s); s = __fmaf_rn(k1, x[j + 5], s); s = __fmaf_rn(k0, x[j + 6], s);
-                o[j] = s;
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float s = __fmul_rn(k0, x[j]);
-                s = __fadd_rn(s, __fmul_rn(k1, x[j + 1])); s = __fadd_rn(s, __fmul_rn(k2, x[j + 2]));
-                s = __fadd_rn(s, __fmul_rn(k3, x[j + 3])); s = __fadd_rn(s, __fmul_rn(k2, x[j + 4]));
-                s = __fadd_rn(s, __fmul_rn(k1, x[j + 5])); s = __fadd_rn(s, __fmul_rn(k0, x[j + 6]));
-                o[j] = s;
-            }
-        }
-        *(float4*)(s_row + rr * VS_TW + 4 * w) = make_float4(o[0], o[1], o[2], o[3]);
+    for (int i = tid; i < BL_ROWS * (VS_TW / 8); i += 256) {
+        const int g = i & 7, rr = i >> 3;                             // s_row row rr <-> gy = y0 - 3 + rr
+        if (y0 - 3 + rr >= H + 3) continue;                           // below every output row of the level
+        const uint2* q = (const uint2*)(s_raw + (rr + 1) * RAW_S + 8 * g);
+        float* dst = s_row + rr * VS_TW + 8 * g;
+        if (x0 + 8 * g < wrow) blur_row_item<true>(q, dst);
+        else blur_row_item<false>(q, dst);
     }
     __syncthreads();
     uint8_t* blur = fpyr + L.blur_off;
     for (int i = tid; i < (VS_TH / 2) * (VS_TW / 4); i += 256) {
         const int w = i & 15, ty = (i >> 4) * 2;                      // two output rows per item
-        const int gx = x0 + 4 * w;
-        if (gx >= L.pitch || y0 + ty >= H) continue;
-        float4 r[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) r[k] = *(const float4*)(s_row + (ty + k) * VS_TW + 4 * w);
-        const bool fma = gx < wcol;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            uint32_t u[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-#define RJ(k) (j == 0 ? r[k].x : j == 1 ? r[k].y : j == 2 ? r[k].z : r[k].w)
-                float s = __fmul_rn(k3, RJ(h + 3));
-                const float p1 = __fadd_rn(RJ(h + 2), RJ(h + 4));
-                const float p2 = __fadd_rn(RJ(h + 1), RJ(h + 5));
-                const float p3 = __fadd_rn(RJ(h + 0), RJ(h + 6));
-#undef RJ
-                if (fma) {
-                    s = __fmaf_rn(k2, p1, s); s = __fmaf_rn(k1, p2, s); s = __fmaf_rn(k0, p3, s);
-                } else {
-                    s = __fadd_rn(s, __fmul_rn(k2, p1)); s = __fadd_rn(s, __fmul_rn(k1, p2));
-                    s = __fadd_rn(s, __fmul_rn(k0, p3));
-                }
-                // round half to even in the mantissa of 1.5 * 2^23 + s  (0 <= s < 255.5)
-                u[j] = __float_as_uint(__fadd_rn(s, 12582912.0f));
-            }
-            const uint32_t packed = __byte_perm(__byte_perm(u[0], u[1], 0x0040), __byte_perm(u[2], u[3], 0x0040), 0x5410);
-            if (y0 + ty + h < H) *(uint32_t*)(blur + (size_t)(y0 + ty + h) * L.pitch + gx) = packed;
-        }
+        const int gx = x0 + 4 * w, gy = y0 + ty;
+        if (gx >= L.pitch || gy >= H) continue;
+        uint32_t o0, o1;
+        if (gx < wcol) blur_col_item<true>(s_row + ty * VS_TW + 4 * w, o0, o1);
+        else blur_col_item<false>(s_row + ty * VS_TW + 4 * w, o0, o1);
+        uint8_t* dst = blur + (size_t)gy * L.pitch + gx;
+        *(uint32_t*)dst = o0;
+        if (gy + 1 < H) *(uint32_t*)(dst + L.pitch) = o1;
     }
 }
 
