@@ -94,3 +94,28 @@ def test_ratio_filter_device_matches_oracle(oracle):
             ref = oracle.match(desc[p][:counts[p]], desc[p + 1][:counts[p + 1]], ratio)
             got = [(int(a), int(b), float(c)) for a, b, c in match[p][:mc[p]]]
             assert got == ref, (p, ratio, len(got), len(ref))
+
+
+def test_frontend_host_chunked_pipeline_equals_unfused(oracle):
+    """vslam_frontend_run_host splits the batch into chunks that overlap copies and compute; every
+    row must equal what separate extract calls + the oracle's matcher give, chunk boundaries included."""
+    from orbslam2._native import OrbHandle
+    from orbslam2.synth import SyntheticVideo
+    v = SyntheticVideo(320, 240, 3)
+    frames = v.frames(0, 40)                                  # 40 frames -> 2 chunks of 20
+    h = OrbHandle(320, 240, n_features=500, max_batch=40)
+    kp, desc, cnt, match, mc = h.frontend_host(frames, 0.75)
+    h1 = OrbHandle(320, 240, n_features=500, max_batch=1)
+    for f in (0, 19, 20, 21, 39):
+        k1, d1, c1 = h1.detect_and_compute_host(frames[f])
+        n = int(c1[0])
+        assert n == int(cnt[f]) and np.array_equal(d1[0][:n], desc[f][:n]) and k1[0][:n].tobytes() == kp[f][:n].tobytes()
+    for p in (0, 18, 19, 20, 38):                             # 19 = the pair across the chunk boundary
+        ref = oracle.match(desc[p][:cnt[p]], desc[p + 1][:cnt[p + 1]], 0.75)
+        got = [(int(a), int(b), float(c)) for a, b, c in match[p][:mc[p]]]
+        assert got == ref, (p, len(got), len(ref))
+    # a batch too small to split takes the same path with one chunk
+    kp2, desc2, cnt2, match2, mc2 = h.frontend_host(frames[:3], 0.75)
+    assert np.array_equal(cnt2, cnt[:3]) and np.array_equal(mc2, mc[:2])
+    assert np.array_equal(match2[0][:mc2[0]], match[0][:mc[0]])
+    h.close(); h1.close()

@@ -203,6 +203,12 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
     cudaError_t e = cudaMemcpy(o->d_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemset(o->d_status, 0, sizeof(int32_t));
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream_in, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream_out, cudaStreamNonBlocking);
+    for (int i = 0; i < VS_HOST_CHUNKS && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&o->ev_in[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_done[i], cudaEventDisableTiming);
+    }
     if (e != cudaSuccess) { vslam_orb_destroy(o); return vs_cuda_fail(e, "orb_create init", __FILE__, __LINE__); }
     *out = o;
     return VSLAM_OK;
@@ -216,6 +222,12 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
                     o->d_knn_dist, o->d_frames, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
+    if (o->stream_in) cudaStreamDestroy(o->stream_in);
+    if (o->stream_out) cudaStreamDestroy(o->stream_out);
+    for (int i = 0; i < VS_HOST_CHUNKS; ++i) {
+        if (o->ev_in[i]) cudaEventDestroy(o->ev_in[i]);
+        if (o->ev_done[i]) cudaEventDestroy(o->ev_done[i]);
+    }
     for (cudaEvent_t e : o->prof_ev) if (e) cudaEventDestroy(e);
     delete o;
     return VSLAM_OK;

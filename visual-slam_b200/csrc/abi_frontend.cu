@@ -128,22 +128,46 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
     VS_REQUIRE(batch >= 1 && batch <= o->prm.max_batch, "batch exceeds max_batch");
     int rc = vs_ensure_host_staging(o);
     if (rc) return rc;
+    VS_REQUIRE(batch == 1 || h_match, "null h_match");
     const VsPlan& p = o->plan;
-    cudaStream_t s = o->stream;
     const size_t fbytes = (size_t)p.width * p.height;
-    VS_CUDA(cudaMemcpyAsync(o->d_frames, h_frames, batch * fbytes, cudaMemcpyHostToDevice, s));
-    rc = vslam_frontend_run(o, o->d_frames, batch, p.width, nullptr, nullptr, ratio, o->d_kp, o->d_desc,
-                            o->d_count, o->d_match, o->d_match_count, s);
-    if (rc) return rc;
-    VS_CUDA(cudaMemcpyAsync(h_kp, o->d_kp, (size_t)batch * p.kp_cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, s));
-    VS_CUDA(cudaMemcpyAsync(h_desc, o->d_desc, (size_t)batch * p.kp_cap * 32, cudaMemcpyDeviceToHost, s));
-    VS_CUDA(cudaMemcpyAsync(h_count, o->d_count, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-    if (batch > 1) {
-        VS_REQUIRE(h_match, "null h_match");
-        VS_CUDA(cudaMemcpyAsync(h_match, o->d_match, (size_t)(batch - 1) * p.kp_cap * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-        VS_CUDA(cudaMemcpyAsync(h_match_count, o->d_match_count, (batch - 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    const size_t cap = p.kp_cap;
+    // Chunked pipeline: the frames of chunk k+1 are copied in (stream_in) and the results of chunk
+    // k-1 copied out (stream_out) while chunk k is computed (stream).  A chunk after the first is
+    // matched against the last frame of its predecessor through the prev-descriptor argument, so the
+    // match rows come out exactly as for one undivided batch.  Host buffers should be pinned.
+    int nchunks = batch / 16;
+    nchunks = nchunks < 1 ? 1 : nchunks > VS_HOST_CHUNKS ? VS_HOST_CHUNKS : nchunks;
+    const int chunk = (batch + nchunks - 1) / nchunks;
+    const int saved_prof = o->prof_on;
+    o->prof_on = 0;   // the per-kernel marks describe one undivided run
+    int k = 0;
+    for (int f0 = 0; f0 < batch; f0 += chunk, ++k) {
+        const int n = batch - f0 < chunk ? batch - f0 : chunk;
+        VS_CUDA(cudaMemcpyAsync(o->d_frames + f0 * fbytes, h_frames + f0 * fbytes, n * fbytes, cudaMemcpyHostToDevice, o->stream_in));
+        VS_CUDA(cudaEventRecord(o->ev_in[k], o->stream_in));
+        VS_CUDA(cudaStreamWaitEvent(o->stream, o->ev_in[k], 0));
+        const int row0 = f0 > 0 ? f0 - 1 : 0;                    // first match row this chunk produces
+        const int rows = f0 > 0 ? n : n - 1;
+        rc = vslam_frontend_run(o, o->d_frames + f0 * fbytes, n, p.width,
+                                f0 > 0 ? o->d_desc + (f0 - 1) * cap * 32 : nullptr, f0 > 0 ? o->d_count + f0 - 1 : nullptr, ratio,
+                                o->d_kp + f0 * cap, o->d_desc + f0 * cap * 32, o->d_count + f0,
+                                o->d_match + row0 * cap * 3, o->d_match_count + row0, o->stream);
+        if (rc) { o->prof_on = saved_prof; return rc; }
+        VS_CUDA(cudaEventRecord(o->ev_done[k], o->stream));
+        VS_CUDA(cudaStreamWaitEvent(o->stream_out, o->ev_done[k], 0));
+        cudaStream_t so = o->stream_out;
+        VS_CUDA(cudaMemcpyAsync(h_kp + f0 * cap, o->d_kp + f0 * cap, n * cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, so));
+        VS_CUDA(cudaMemcpyAsync(h_desc + f0 * cap * 32, o->d_desc + f0 * cap * 32, n * cap * 32, cudaMemcpyDeviceToHost, so));
+        VS_CUDA(cudaMemcpyAsync(h_count + f0, o->d_count + f0, n * sizeof(int32_t), cudaMemcpyDeviceToHost, so));
+        if (rows > 0) {
+            VS_CUDA(cudaMemcpyAsync(h_match + row0 * cap * 3, o->d_match + row0 * cap * 3, rows * cap * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, so));
+            VS_CUDA(cudaMemcpyAsync(h_match_count + row0, o->d_match_count + row0, rows * sizeof(int32_t), cudaMemcpyDeviceToHost, so));
+        }
     }
-    VS_CUDA(cudaStreamSynchronize(s));
+    o->prof_on = saved_prof;
+    VS_CUDA(cudaStreamSynchronize(o->stream_out));
+    VS_CUDA(cudaStreamSynchronize(o->stream));
     return vslam_orb_last_status(o);
 }
 

@@ -76,6 +76,8 @@ struct VsPlan {
 #define VS_PROF_SLOTS 24
 #define VS_PROF_MAX_MARKS 64
 
+#define VS_HOST_CHUNKS 8
+
 struct vslam_orb {
     vslam_orb_params prm;
     VsPlan plan;
@@ -99,6 +101,9 @@ struct vslam_orb {
     int32_t* d_match_count;
     int frame_pitch;
     cudaStream_t stream;       // own stream for *_host calls
+    // chunked host pipeline (vslam_frontend_run_host): copy-in / copy-out streams and per-chunk events
+    cudaStream_t stream_in, stream_out;
+    cudaEvent_t ev_in[VS_HOST_CHUNKS], ev_done[VS_HOST_CHUNKS];
     cudaStream_t last_stream;
     const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)
     int last_pitch, last_batch;
