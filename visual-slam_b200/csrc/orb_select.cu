@@ -243,33 +243,45 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
-// IC angle of the radius-15 disc around (x0, y0); all 32 lanes of a warp take part.
-__device__ __forceinline__ float ic_angle_warp(const uint8_t* img, int pitch, int x0, int y0, int lane)
+// rBRIEF pattern as float4 {x0,y0,x1,y1}, transposed: lane j (descriptor byte j) reads test 8j+t
+// at [t*32 + j] with one coalesced 128-bit load (4 KB, L1 resident)
+__device__ const float4 g_patf_t[256] = {
+#include "rbrief_pattern_t.inc"
+};
+
+#define DESC_R 18                     // blurred window radius: a rotated pattern point stays within |(13,13)| = 18.4
+#define DESC_WIN (2 * DESC_R + 1)     // 37 rows
+#define DESC_WIN_S 40                 // bytes per row (37 + up to 3 of alignment slack)
+#define IC_WIN (2 * VS_HALF_PATCH + 1)   // 31 rows of the unblurred level for the intensity centroid
+#define IC_WIN_S 36                   // bytes per row (31 + up to 3 of alignment slack)
+
+// Copy a rows x (4*words)-byte window starting at the 4-byte aligned column xs of row ys into shared
+// memory.  Lane = (row group, word): the row pointer advances by a fixed stride, no per-load index math.
+template <int ROWS, int WORDS>
+__device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, int pitch, int xs, int ys, int lane,
+                                             bool aligned)
 {
-    const int u = lane - VS_HALF_PATCH;    // lanes 0..30 <-> columns -15..15
-    int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int au = abs(u);
-        const uint8_t* c = img + (size_t)y0 * pitch + x0 + u;
-        int col = 0, vs = 0;
+    constexpr int RG = 32 / WORDS;                  // rows per pass
+    const int r0 = lane / WORDS, cw = lane - r0 * WORDS;
+    if (r0 >= RG) return;
+    const uint8_t* src = img + (size_t)(ys + r0) * pitch + xs + 4 * cw;
+    uint32_t* dst = (uint32_t*)win + r0 * WORDS + cw;
+    const size_t step = (size_t)pitch * RG;
 #pragma unroll
-        for (int v = -VS_HALF_PATCH; v <= VS_HALF_PATCH; ++v) {
-            if (au <= c_umax[v < 0 ? -v : v]) {
-                int val = __ldg(c + (ptrdiff_t)v * pitch);
-                col += val;
-                vs += v * val;
-            }
+    for (int r = 0; r < ROWS; r += RG) {
+        if (r + r0 < ROWS) {
+            uint32_t v;
+            if (aligned) v = __ldg((const uint32_t*)src);
+            else v = (uint32_t)__ldg(src) | ((uint32_t)__ldg(src + 1) << 8) | ((uint32_t)__ldg(src + 2) << 16) | ((uint32_t)__ldg(src + 3) << 24);
+            dst[r * WORDS] = v;
         }
-        m10 = u * col;
-        m01 = vs;
+        src += step;
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    return fast_atan2_deg((float)m01, (float)m10);
 }
+
+// One warp per keypoint, VS_DESC_PER_WARP keypoints in turn.  Keypoints are at least 31 px inside
+// their level, so both windows lie inside the image.
+#define VS_DESC_PER_WARP 4
 
 __global__ void __launch_bounds__(256)
 vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frames, int fpitch,
@@ -277,41 +289,96 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
                    const int32_t* __restrict__ counters, vslam_keypoint* __restrict__ kp_out,
                    uint8_t* __restrict__ desc_out, int32_t* __restrict__ count_out)
 {
-    __shared__ uint32_t s_pat[256];
-    load_pattern(s_pat);
-    __syncthreads();
-    const int b = blockIdx.y, lane = threadIdx.x & 31;
-    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    __shared__ __align__(16) uint8_t s_blur[8][DESC_WIN * DESC_WIN_S];
+    __shared__ __align__(16) uint8_t s_raw[8][IC_WIN * IC_WIN_S];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int32_t* ctr = counters + (size_t)b * plan.n_levels * VS_CTR_STRIDE;
-    int level = -1, j = 0, total = 0;
-    for (int l = 0; l < plan.n_levels; ++l) {
-        int n = ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL];
-        if (level < 0 && i < total + n) { level = l; j = i - total; }
-        total += n;
+    // start of each level's keypoints in the frame's output rows
+    int nfin[VS_MAX_LEVELS], total = 0;
+#pragma unroll
+    for (int l = 0; l < VS_MAX_LEVELS; ++l) {
+        nfin[l] = l < plan.n_levels ? ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL] : 0;
+        total += nfin[l];
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) count_out[b] = total;
-    if (level < 0 || i >= plan.kp_cap) return;
-    const VsLevel& L = plan.lv[level];
-    VsCand c = stage[(size_t)b * plan.stage_frame_entries + L.stage_off + j];
     const uint8_t* fp = pyr + (size_t)b * plan.pyr_frame_bytes;
-    const uint8_t* raw;
-    int rpitch;
-    if (level == 0) { raw = frames + (size_t)b * fstride; rpitch = fpitch; }
-    else { raw = fp + L.raw_off; rpitch = L.pitch; }
-    const float ang = ic_angle_warp(raw, rpitch, c.x, c.y, lane);
-    const float kx = __fmul_rn((float)c.x, L.scale), ky = __fmul_rn((float)c.y, L.scale);
-    vslam_keypoint* ko = kp_out + (size_t)b * plan.kp_cap + i;
-    if (lane == 0) {
-        ko->x = kx; ko->y = ky; ko->size = __fmul_rn(31.f, L.scale);
-        ko->angle = ang; ko->response = __uint_as_float(c.v); ko->octave = level;
+    uint8_t* wb = s_blur[wid];
+    uint8_t* wr = s_raw[wid];
+    const int u = lane - VS_HALF_PATCH;              // lanes 0..30 <-> columns -15..15 of the disc
+    const int vmax = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;   // the disc is symmetric: |v| <= umax[|u|]
+
+    for (int k = 0; k < VS_DESC_PER_WARP; ++k) {
+        const int i = (blockIdx.x * 8 + wid) * VS_DESC_PER_WARP + k;
+        if (i >= total || i >= plan.kp_cap) break;
+        int level = 0, j = i;
+#pragma unroll
+        for (int l = 0; l < VS_MAX_LEVELS - 1; ++l)
+            if (level == l && j >= nfin[l]) { j -= nfin[l]; level = l + 1; }
+        const VsLevel& L = plan.lv[level];
+        const VsCand c = stage[(size_t)b * plan.stage_frame_entries + L.stage_off + j];
+        const uint8_t* raw;
+        int rpitch;
+        if (level == 0) { raw = frames + (size_t)b * fstride; rpitch = fpitch; }
+        else { raw = fp + L.raw_off; rpitch = L.pitch; }
+        // ---- intensity-centroid angle (K6) on the unblurred level
+        const int x0 = c.x, y0 = c.y;
+        const int rxs = (x0 - VS_HALF_PATCH) & ~3;
+        __syncwarp();
+        stage_window<IC_WIN, IC_WIN_S / 4>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane,
+                                            (((size_t)raw | (size_t)rpitch) & 3) == 0);
+        __syncwarp();
+        int m10 = 0, m01 = 0;
+        {
+            const uint8_t* cc = wr + VS_HALF_PATCH * IC_WIN_S + (x0 - rxs) + u;   // centre row, this lane's column
+            int col = vmax >= 0 ? cc[0] : 0, vs = 0;
+#pragma unroll
+            for (int v = 1; v <= VS_HALF_PATCH; ++v) {
+                if (v <= vmax) {
+                    const int lo = cc[-v * IC_WIN_S], hi = cc[v * IC_WIN_S];
+                    col += lo + hi;
+                    vs += v * (hi - lo);
+                }
+            }
+            m10 = u * col;
+            m01 = vs;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        }
+        const float ang = fast_atan2_deg((float)m01, (float)m10);
+        const float kx = __fmul_rn((float)x0, L.scale), ky = __fmul_rn((float)y0, L.scale);
+        if (lane == 0) {
+            vslam_keypoint* ko = kp_out + (size_t)b * plan.kp_cap + i;
+            ko->x = kx; ko->y = ky; ko->size = __fmul_rn(31.f, L.scale);
+            ko->angle = ang; ko->response = __uint_as_float(c.v); ko->octave = level;
+        }
+        // ---- steered rBRIEF (K7b): centre cvRound(pt * (1/scale)), rotation from the angle in radians
+        const float inv = __fdiv_rn(1.f, L.scale);
+        const int cx = __float2int_rn(__fmul_rn(kx, inv)), cy = __float2int_rn(__fmul_rn(ky, inv));
+        const float rad = __fmul_rn(ang, (float)(3.14159265358979323846 / 180.f));
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        const float ca = (float)cd, sa = (float)sd;
+        const int xs = (cx - DESC_R) & ~3;
+        stage_window<DESC_WIN, DESC_WIN_S / 4>(wb, fp + L.blur_off, L.pitch, xs, cy - DESC_R, lane, true);
+        __syncwarp();
+        // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
+        const float magic = 12582912.0f;
+        const uint32_t off0 = (uint32_t)(DESC_R * DESC_WIN_S + (cx - xs)) - 0x4B400000u * (DESC_WIN_S + 1);
+        uint32_t byte = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const float4 p = __ldg(&g_patf_t[t * 32 + lane]);
+            const float fx0 = __fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), fy0 = __fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca));
+            const float fx1 = __fsub_rn(__fmul_rn(p.z, ca), __fmul_rn(p.w, sa)), fy1 = __fadd_rn(__fmul_rn(p.z, sa), __fmul_rn(p.w, ca));
+            const uint32_t i0 = __float_as_uint(__fadd_rn(fy0, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
+            const uint32_t i1 = __float_as_uint(__fadd_rn(fy1, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
+            byte |= (uint32_t)(wb[i0] < wb[i1]) << t;
+        }
+        desc_out[((size_t)b * plan.kp_cap + i) * 32 + lane] = (uint8_t)byte;
     }
-    // descriptor centre cvRound(pt * (1/scale)), rotation from the angle in radians
-    const float inv = __fdiv_rn(1.f, L.scale);
-    const int cx = __float2int_rn(__fmul_rn(kx, inv)), cy = __float2int_rn(__fmul_rn(ky, inv));
-    const float rad = __fmul_rn(ang, (float)(3.14159265358979323846 / 180.f));
-    const float ca = (float)cos((double)rad), sa = (float)sin((double)rad);
-    uint32_t byte = brief_byte(fp + L.blur_off, raw, L.w, L.h, L.pitch, rpitch, cx, cy, ca, sa, s_pat, lane);
-    desc_out[((size_t)b * plan.kp_cap + i) * 32 + lane] = (uint8_t)byte;
 }
 
 void vs_configure_select_smem(int bytes)
@@ -338,7 +405,7 @@ int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
                                                                o->d_counters, o->d_status);
     vs_prof_mark(o, VS_PROF_DESCRIBE, s);
     ++g_vs_launches;
-    vs_describe_kernel<<<dim3((p.kp_cap + 7) / 8, batch), 256, 0, s>>>(
+    vs_describe_kernel<<<dim3((p.kp_cap + 8 * VS_DESC_PER_WARP - 1) / (8 * VS_DESC_PER_WARP), batch), 256, 0, s>>>(
         p, d_frames, pitch, fstride, o->d_pyr, o->d_stage, o->d_counters, d_kp, d_desc, d_count);
     vs_prof_mark(o, -1, s);
     VS_CUDA(cudaGetLastError());
