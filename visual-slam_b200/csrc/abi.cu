@@ -205,8 +205,10 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream_in, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream_out, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&o->stream2, cudaStreamNonBlocking);
     for (int i = 0; i < VS_HOST_CHUNKS && e == cudaSuccess; ++i) {
         e = cudaEventCreateWithFlags(&o->ev_in[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_ext[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_done[i], cudaEventDisableTiming);
     }
     if (e != cudaSuccess) { vslam_orb_destroy(o); return vs_cuda_fail(e, "orb_create init", __FILE__, __LINE__); }
@@ -224,8 +226,10 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     if (o->stream) cudaStreamDestroy(o->stream);
     if (o->stream_in) cudaStreamDestroy(o->stream_in);
     if (o->stream_out) cudaStreamDestroy(o->stream_out);
+    if (o->stream2) cudaStreamDestroy(o->stream2);
     for (int i = 0; i < VS_HOST_CHUNKS; ++i) {
         if (o->ev_in[i]) cudaEventDestroy(o->ev_in[i]);
+        if (o->ev_ext[i]) cudaEventDestroy(o->ev_ext[i]);
         if (o->ev_done[i]) cudaEventDestroy(o->ev_done[i]);
     }
     for (cudaEvent_t e : o->prof_ev) if (e) cudaEventDestroy(e);

@@ -4,6 +4,9 @@
 #include "common.cuh"
 
 int vs_ensure_host_staging(vslam_orb* o);
+int vs_frontend_match(vslam_orb* o, int batch, const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
+                      const uint8_t* d_desc, const int32_t* d_count, int32_t* d_match, int32_t* d_match_count,
+                      cudaStream_t s);
 int vs_launch_match_masked(const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, const uint8_t* d_mask,
                            int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
 
@@ -94,7 +97,17 @@ extern "C" int vslam_frontend_run(vslam_orb* o, const uint8_t* d_frames, int bat
     VS_REQUIRE(!d_prev_desc || d_prev_count, "d_prev_count required with d_prev_desc");
     int rc = vslam_orb_detect_and_compute(o, d_frames, batch, pitch, d_kp, d_desc, d_count, stream);
     if (rc) return rc;
-    cudaStream_t s = (cudaStream_t)stream;
+    return vs_frontend_match(o, batch, d_prev_desc, d_prev_count, ratio, d_desc, d_count, d_match, d_match_count,
+                             (cudaStream_t)stream);
+}
+
+// matching half of the front end: pair 0 = (previous boundary frame, frame 0) when given, then
+// pair i = (frame i, frame i+1)
+int vs_frontend_match(vslam_orb* o, int batch, const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
+                      const uint8_t* d_desc, const int32_t* d_count, int32_t* d_match, int32_t* d_match_count,
+                      cudaStream_t s)
+{
+    int rc;
     const int cap = o->plan.kp_cap;
     int32_t* m = d_match;
     int32_t* mc = d_match_count;
@@ -133,9 +146,11 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
     const size_t fbytes = (size_t)p.width * p.height;
     const size_t cap = p.kp_cap;
     // Chunked pipeline: the frames of chunk k+1 are copied in (stream_in) and the results of chunk
-    // k-1 copied out (stream_out) while chunk k is computed (stream).  A chunk after the first is
-    // matched against the last frame of its predecessor through the prev-descriptor argument, so the
-    // match rows come out exactly as for one undivided batch.  Host buffers should be pinned.
+    // k-1 copied out (stream_out) while chunk k is computed.  Chunks alternate between two compute
+    // streams on disjoint slices of the workspace, so that the tail of one chunk's kernels overlaps
+    // the head of the next.  A chunk after the first is matched against the last frame of its
+    // predecessor (its descriptors are ready at ev_ext[k-1]), so the match rows come out exactly as
+    // for one undivided batch.  Host buffers should be pinned.
     int nchunks = batch / 16;
     nchunks = nchunks < 1 ? 1 : nchunks > VS_HOST_CHUNKS ? VS_HOST_CHUNKS : nchunks;
     const int chunk = (batch + nchunks - 1) / nchunks;
@@ -144,17 +159,31 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
     int k = 0;
     for (int f0 = 0; f0 < batch; f0 += chunk, ++k) {
         const int n = batch - f0 < chunk ? batch - f0 : chunk;
+        cudaStream_t cs = (k & 1) ? o->stream2 : o->stream;
         VS_CUDA(cudaMemcpyAsync(o->d_frames + f0 * fbytes, h_frames + f0 * fbytes, n * fbytes, cudaMemcpyHostToDevice, o->stream_in));
         VS_CUDA(cudaEventRecord(o->ev_in[k], o->stream_in));
-        VS_CUDA(cudaStreamWaitEvent(o->stream, o->ev_in[k], 0));
+        VS_CUDA(cudaStreamWaitEvent(cs, o->ev_in[k], 0));
+        // view of the handle whose workspace starts at frame slot f0
+        vslam_orb view = *o;
+        view.d_pyr += f0 * p.pyr_frame_bytes;
+        view.d_cand += f0 * p.cand_frame_entries;
+        view.d_stage += f0 * p.stage_frame_entries;
+        view.d_counters += (size_t)f0 * p.n_levels * VS_CTR_STRIDE;
+        view.d_knn_idx += f0 * cap * 2;
+        view.d_knn_dist += f0 * cap * 2;
+        view.knn_no_split = 1;
+        rc = vslam_orb_detect_and_compute(&view, o->d_frames + f0 * fbytes, n, p.width, o->d_kp + f0 * cap,
+                                          o->d_desc + f0 * cap * 32, o->d_count + f0, cs);
+        if (rc) { o->prof_on = saved_prof; return rc; }
+        VS_CUDA(cudaEventRecord(o->ev_ext[k], cs));
+        if (k > 0) VS_CUDA(cudaStreamWaitEvent(cs, o->ev_ext[k - 1], 0));
         const int row0 = f0 > 0 ? f0 - 1 : 0;                    // first match row this chunk produces
         const int rows = f0 > 0 ? n : n - 1;
-        rc = vslam_frontend_run(o, o->d_frames + f0 * fbytes, n, p.width,
-                                f0 > 0 ? o->d_desc + (f0 - 1) * cap * 32 : nullptr, f0 > 0 ? o->d_count + f0 - 1 : nullptr, ratio,
-                                o->d_kp + f0 * cap, o->d_desc + f0 * cap * 32, o->d_count + f0,
-                                o->d_match + row0 * cap * 3, o->d_match_count + row0, o->stream);
+        rc = vs_frontend_match(&view, n, f0 > 0 ? o->d_desc + (f0 - 1) * cap * 32 : nullptr,
+                               f0 > 0 ? o->d_count + f0 - 1 : nullptr, ratio, o->d_desc + f0 * cap * 32, o->d_count + f0,
+                               o->d_match + row0 * cap * 3, o->d_match_count + row0, cs);
         if (rc) { o->prof_on = saved_prof; return rc; }
-        VS_CUDA(cudaEventRecord(o->ev_done[k], o->stream));
+        VS_CUDA(cudaEventRecord(o->ev_done[k], cs));
         VS_CUDA(cudaStreamWaitEvent(o->stream_out, o->ev_done[k], 0));
         cudaStream_t so = o->stream_out;
         VS_CUDA(cudaMemcpyAsync(h_kp + f0 * cap, o->d_kp + f0 * cap, n * cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, so));
@@ -164,10 +193,12 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
             VS_CUDA(cudaMemcpyAsync(h_match + row0 * cap * 3, o->d_match + row0 * cap * 3, rows * cap * 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, so));
             VS_CUDA(cudaMemcpyAsync(h_match_count + row0, o->d_match_count + row0, rows * sizeof(int32_t), cudaMemcpyDeviceToHost, so));
         }
+        o->last_stream = cs;
     }
     o->prof_on = saved_prof;
     VS_CUDA(cudaStreamSynchronize(o->stream_out));
     VS_CUDA(cudaStreamSynchronize(o->stream));
+    VS_CUDA(cudaStreamSynchronize(o->stream2));
     return vslam_orb_last_status(o);
 }
 

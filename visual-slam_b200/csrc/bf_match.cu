@@ -312,7 +312,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     // split the train range only when the grid would not fill the 148 SMs a few times over
     int nsplit = 1;
     const long want = 148L * 8;
-    if ((long)qtiles * pairs < want && ttiles > 1) {
+    if ((long)qtiles * pairs < want && ttiles > 1 && !(prof && prof->knn_no_split)) {
         nsplit = (int)((want + (long)qtiles * pairs - 1) / ((long)qtiles * pairs));
         if (nsplit > ttiles) nsplit = ttiles;
         if (nsplit > 64) nsplit = 64;

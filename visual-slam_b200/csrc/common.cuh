@@ -102,8 +102,9 @@ struct vslam_orb {
     int frame_pitch;
     cudaStream_t stream;       // own stream for *_host calls
     // chunked host pipeline (vslam_frontend_run_host): copy-in / copy-out streams and per-chunk events
-    cudaStream_t stream_in, stream_out;
-    cudaEvent_t ev_in[VS_HOST_CHUNKS], ev_done[VS_HOST_CHUNKS];
+    cudaStream_t stream_in, stream_out, stream2;   // stream / stream2 alternate between compute chunks
+    cudaEvent_t ev_in[VS_HOST_CHUNKS], ev_ext[VS_HOST_CHUNKS], ev_done[VS_HOST_CHUNKS];
+    int knn_no_split;          // set on the per-chunk views: the split-train scratch of kNN-2 is not per stream
     cudaStream_t last_stream;
     const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)
     int last_pitch, last_batch;
