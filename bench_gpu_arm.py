@@ -11,7 +11,7 @@ def run_gpu_arm(args, rank, world, B):
     import torch
     import torch.distributed as dist
     import bench as BN
-    from orbslam2 import _native
+    from orbslam2 import _native, sharding
     from orbslam2.synth import SyntheticVideo
 
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -74,12 +74,7 @@ def run_gpu_arm(args, rank, world, B):
             return []
         first_desc.copy_(desc[0])
         first_count.copy_(count[0:1])
-        ops = []
-        if rank > 0:
-            ops += [dist.P2POp(dist.isend, first_desc, rank - 1), dist.P2POp(dist.isend, first_count, rank - 1)]
-        if rank < world - 1:
-            ops += [dist.P2POp(dist.irecv, nb_desc, rank + 1), dist.P2POp(dist.irecv, nb_count, rank + 1)]
-        return dist.batch_isend_irecv(ops) if ops else []
+        return sharding.boundary_exchange(dist, rank, world, first_desc, first_count, nb_desc, nb_count)
 
     def boundary_match():
         if world == 1 or rank == world - 1:
@@ -136,9 +131,7 @@ def run_gpu_arm(args, rank, world, B):
     L.vslam_orb_set_profiling(orb.handle, 0)
     launches = L.vslam_launch_count() - launches0
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms = float(sharding.max_over_ranks(dist, world, t).item())
     value = world * B * K / (ms * 1e-3)
     n_kp = int(count.clamp(max=cap).sum().item())
     n_match = int(mcount.sum().item())
@@ -165,9 +158,7 @@ def run_gpu_arm(args, rank, world, B):
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_fps = world * B * Ke / float(t.item())
+    e2e_fps = world * B * Ke / float(sharding.max_over_ranks(dist, world, t).item())
     h2d = B * w * h
     d2h = B * cap * (24 + 32) + B * 4 + (B - 1) * (cap * 12 + 4)
 

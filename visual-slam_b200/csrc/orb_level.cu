@@ -23,6 +23,9 @@
 #define SC_H (VS_TH + 2)              // score rows  y0-1 .. y0+TH
 #define SC_S 72                       // score row stride; column index = tx + 4
 #define BL_ROWS (VS_TH + 6)
+#ifndef VS_LEVEL_CTAS
+#define VS_LEVEL_CTAS 4                // resident CTAs per SM the register budget is capped for (5 spills, no faster)
+#endif
 #define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
 
 // getGaussianKernel(7, 2, CV_32F) of cv2 4.13, taps outer..centre (bit patterns)
@@ -95,15 +98,10 @@ __device__ __forceinline__ int fast_single(const uint16_t* p, int thr)
 
 __device__ __forceinline__ uint32_t fsr16(uint32_t lo, uint32_t hi) { return __funnelshift_r(lo, hi, 16); }
 
-// exact u16 -> float without the conversion pipe: 2^23 + v has v in its low mantissa bits
-__device__ __forceinline__ float lane_lo_f(uint32_t w)
-{
-    return __fadd_rn(__uint_as_float((w & 0xffffu) | 0x4B000000u), -8388608.0f);
-}
-__device__ __forceinline__ float lane_hi_f(uint32_t w)
-{
-    return __fadd_rn(__uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632)), -8388608.0f);
-}
+// u16 lane -> float: I2F.U16 takes either half of a register directly (XU pipe, which is otherwise
+// idle here; the ALU pipe is the one this kernel saturates)
+__device__ __forceinline__ float lane_lo_f(uint32_t w) { return (float)(uint16_t)w; }
+__device__ __forceinline__ float lane_hi_f(uint32_t w) { return (float)(uint16_t)(w >> 16); }
 
 // four source bytes at column gx of a row, byte-wise with REFLECT_101 (words that are not
 // wholly inside the row, or rows that are not 4-byte aligned)
@@ -182,7 +180,7 @@ __device__ __forceinline__ void blur_col_item(const float* p, uint32_t& out0, ui
     }
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, VS_LEVEL_CTAS)
 vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* __restrict__ frames,
                 int fpitch, size_t fstride, uint8_t* __restrict__ pyr,
                 const uint32_t* __restrict__ tab, VsCand* __restrict__ cand,
