@@ -169,6 +169,16 @@ def run_gpu_arm(args, rank, world, B):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        # measured DRAM traffic of the level launches of one step (ncu --set full capture committed under
+        # profiles/); only quoted when it was taken on this workload and batch
+        traffic, traffic_src = None, None
+        try:
+            tj = json.load(open(os.path.join(BN.ROOT, "profiles", "r1_level_traffic.json")))
+            if tj.get("workload") == args.workload and int(tj.get("frames_per_step", 0)) == B:
+                traffic = int(tj["dram_read_bytes"]) + int(tj["dram_write_bytes"])
+                traffic_src = tj.get("source")
+        except Exception:
+            pass
         level_ms = float(prof[:16].sum())
         lvl_bytes = BN.level_kernel_bytes(w, h) * B * K
         achieved = lvl_bytes / (level_ms * 1e-3) / 1e9 if level_ms > 0 else 0.0
@@ -191,14 +201,19 @@ def run_gpu_arm(args, rank, world, B):
                          "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": achieved / hbm_peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                         "algorithmic_bytes_per_frame": BN.level_kernel_bytes(w, h), "traffic": None,
+                         "algorithmic_bytes_per_frame": BN.level_kernel_bytes(w, h),
+                         "algorithmic_bytes_per_step": BN.level_kernel_bytes(w, h) * B, "traffic": traffic,
+                         "traffic_note": traffic_src,
                          "ms_per_step": level_ms / K},
             "extraction": {"ms_per_step": float(prof[:19].sum()) / K,
                            "algorithmic_bytes_per_frame": BN.extraction_bytes(w, h, nf),
                            "achieved_gbs": BN.extraction_bytes(w, h, nf) * B * K / (prof[:19].sum() * 1e-3) / 1e9
                            if prof[:19].sum() > 0 else 0.0},
             "matching": {"ms_per_step": float(prof[19] + prof[20]) / K, "gpairs_per_s": pairs_per_s / 1e9,
-                         "popc32_per_s": 8 * pairs_per_s},
+                         # kNN-2 runs on the int8 MMA pipe: 16 descriptor pairs per IMMA.16832; peak = 0.12 IMMA/clk/SMSP
+                         # measured by scratch/ubench/imma.cu on this pool's B200 (148 SMs x 4 SMSPs x 1.965 GHz)
+                         "imma_per_s": pairs_per_s / 16.0, "imma_peak_per_s": 0.12 * 592 * 1.965e9,
+                         "imma_frac": pairs_per_s / 16.0 / (0.12 * 592 * 1.965e9)},
             "kernel_ms_per_step": breakdown,
         }
         if world == 1 and not args.no_cpu:
