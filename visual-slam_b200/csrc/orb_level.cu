@@ -70,6 +70,18 @@ __device__ __forceinline__ uint32_t fast_pair(const uint32_t (&v)[16], uint32_t 
     return m - 0x02000200u;                  // max(S - thr, 0) per lane
 }
 
+// Compass pre-test for a pixel pair: a, b, c, d = the circle points (0,+3), (0,-3), (+3,0), (-3,0), cen = centre.
+// Returns bit 15 / 31 set for the lanes whose second-largest compass value exceeds cen + thr or whose
+// second-smallest is below cen - thr (necessary for a FAST-9 corner).
+__device__ __forceinline__ uint32_t compass_need(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t cen, uint32_t kbias)
+{
+    const uint32_t mn1 = __vminu2(a, b), mx1 = __vmaxu2(a, b), mn2 = __vminu2(c, d), mx2 = __vmaxu2(c, d);
+    const uint32_t sl = __vimax3_u16x2(mn1, mn2, __vminu2(mx1, mx2));      // second largest
+    const uint32_t ss = __vimin3_u16x2(mx1, mx2, __vmaxu2(mn1, mn2));      // second smallest
+    const uint32_t m = __vmaxu2((sl + kbias) - cen, (cen + kbias) - ss);  // max(sl - cen, cen - ss) - thr + 512
+    return ((m + 0x7fff7fffu) - 0x02000200u) & 0x80008000u;               // lanes with m > 512
+}
+
 // one pixel (ring columns of the tile); p points into the 16-bit tile
 __device__ __forceinline__ int fast_single(const uint16_t* p, int thr)
 {
@@ -186,7 +198,11 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 const uint32_t* __restrict__ tab, VsCand* __restrict__ cand,
                 int32_t* __restrict__ counters)
 {
-    __shared__ __align__(16) uint16_t s_raw[RAW_H * RAW_S];
+    // 8 elements of front padding: the networks of the ring column read one word left of row 0
+    __shared__ __align__(16) uint16_t s_raw_store[RAW_H * RAW_S + 8];
+    uint16_t* const s_raw = s_raw_store + 8;
+    __shared__ uint16_t s_queue[SC_H * (VS_TW / 2 + 2)];   // (row << 6) | word of the pixel pairs that pass the pre-test
+    __shared__ int s_nq;
     __shared__ __align__(16) uint16_t s_sc[SC_H * SC_S];   // max(S - thr, 0), 16-bit lanes
     __shared__ __align__(16) float s_row[BL_ROWS * VS_TW];
     __shared__ uint32_t s_hist[256];
@@ -204,7 +220,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     uint8_t* fpyr = pyr + (size_t)b * plan.pyr_frame_bytes;
 
     s_hist[tid] = 0;
-    if (tid == 0) s_n = 0;
+    if (tid == 0) { s_n = 0; s_nq = 0; }
 
     // ---- 1. raw tile (16-bit lanes) ------------------------------------------
     if (level == 0) {
@@ -344,73 +360,73 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     const int thr = plan.fast_thr;
     const uint32_t kbias = (uint32_t)(512 - thr) * 0x00010001u;
     const int cx_lo = VS_EDGE - 1, cx_hi = W - VS_EDGE, cy_lo = VS_EDGE - 1, cy_hi = H - VS_EDGE;
+    // 3a. compass pre-test.  Any arc of 9 contains at least two of the four compass points, so a corner
+    // needs its second-largest compass value above c + thr or its second-smallest below c - thr.  Pixel
+    // pairs that pass are queued; the full min/max networks (3b) then run on whole warps of queued pairs
+    // only (a third to a half of the pairs on textured images) instead of on every pixel.
     for (int i = tid; i < SC_H * (VS_TW / 4); i += 256) {
         const int w = i & 15, r = i >> 4;
         const int gy = y0 - 1 + r, gx = x0 + 4 * w;
-        uint32_t oA = 0, oB = 0;
+        uint32_t needA = 0, needB = 0;
         if (gy >= cy_lo && gy <= cy_hi && gx + 3 >= cx_lo && gx <= cx_hi) {
             const uint16_t* base = s_raw + (r + 3) * RAW_S + 4 * w;   // word 2 of this row = pixels 0,1
-            uint32_t vA[16], vB[16], cA, cB;
-            {
-                const uint2* q = (const uint2*)(base + 3 * RAW_S);
-                uint32_t w1 = q[0].y, w2 = q[1].x, w3 = q[1].y, w4 = q[2].x;
-                vA[0] = w2; vB[0] = w3;
-                vA[1] = fsr16(w2, w3); vB[1] = fsr16(w3, w4);
-                vA[15] = fsr16(w1, w2); vB[15] = vA[1];
-            }
-            {
-                const uint2* q = (const uint2*)(base - 3 * RAW_S);
-                uint32_t w1 = q[0].y, w2 = q[1].x, w3 = q[1].y, w4 = q[2].x;
-                vA[8] = w2; vB[8] = w3;
-                vA[7] = fsr16(w2, w3); vB[7] = fsr16(w3, w4);
-                vA[9] = fsr16(w1, w2); vB[9] = vA[7];
-            }
-            {
-                const uint2* q = (const uint2*)(base + 2 * RAW_S);
-                vA[14] = q[0].y; vB[14] = q[1].x; vA[2] = q[1].y; vB[2] = q[2].x;
-            }
-            {
-                const uint2* q = (const uint2*)(base - 2 * RAW_S);
-                vA[10] = q[0].y; vB[10] = q[1].x; vA[6] = q[1].y; vB[6] = q[2].x;
-            }
-            {
-                const uint2* q = (const uint2*)(base + RAW_S);
-                uint2 a = q[0], m = q[1], e = q[2];
-                vA[3] = fsr16(m.y, e.x); vB[3] = fsr16(e.x, e.y);
-                vA[13] = fsr16(a.x, a.y); vB[13] = fsr16(a.y, m.x);
-            }
-            {
-                const uint2* q = (const uint2*)(base - RAW_S);
-                uint2 a = q[0], m = q[1], e = q[2];
-                vA[5] = fsr16(m.y, e.x); vB[5] = fsr16(e.x, e.y);
-                vA[11] = fsr16(a.x, a.y); vB[11] = fsr16(a.y, m.x);
-            }
-            {
-                const uint2* q = (const uint2*)base;
-                uint2 a = q[0], m = q[1], e = q[2];
-                vA[4] = fsr16(m.y, e.x); vB[4] = fsr16(e.x, e.y);
-                vA[12] = fsr16(a.x, a.y); vB[12] = fsr16(a.y, m.x);
-                cA = m.x; cB = m.y;
-            }
-            oA = fast_pair(vA, cA, kbias);
-            oB = fast_pair(vB, cB, kbias);
-            if (gx < cx_lo || gx + 3 > cx_hi) {
-                if (gx + 0 < cx_lo || gx + 0 > cx_hi) oA &= 0xffff0000u;
-                if (gx + 1 < cx_lo || gx + 1 > cx_hi) oA &= 0x0000ffffu;
-                if (gx + 2 < cx_lo || gx + 2 > cx_hi) oB &= 0xffff0000u;
-                if (gx + 3 < cx_lo || gx + 3 > cx_hi) oB &= 0x0000ffffu;
-            }
+            const uint2 up = *(const uint2*)(base + 3 * RAW_S + 4), dn = *(const uint2*)(base - 3 * RAW_S + 4);
+            const uint2* q = (const uint2*)base;
+            const uint2 a = q[0], m = q[1], e = q[2];
+            needA = compass_need(up.x, dn.x, fsr16(m.y, e.x), fsr16(a.x, a.y), m.x, kbias);
+            needB = compass_need(up.y, dn.y, fsr16(e.x, e.y), fsr16(a.y, m.x), m.y, kbias);
         }
-        *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(oA, oB);
+        *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(0u, 0u);
+        // warp-aggregated push of (row, word) entries
+        const uint32_t mA = __ballot_sync(0xffffffffu, needA != 0), mB = __ballot_sync(0xffffffffu, needB != 0);
+        if (mA | mB) {
+            const int lane = tid & 31, nA = __popc(mA);
+            int basepos = 0;
+            if (lane == 0) basepos = atomicAdd(&s_nq, nA + __popc(mB));
+            basepos = __shfl_sync(0xffffffffu, basepos, 0);
+            const uint32_t lt = (1u << lane) - 1u;
+            if (needA) s_queue[basepos + __popc(mA & lt)] = (uint16_t)((r << 6) | (2 * w + 2));
+            if (needB) s_queue[basepos + nA + __popc(mB & lt)] = (uint16_t)((r << 6) | (2 * w + 3));
+        }
     }
-    if (tid < 2 * SC_H) {   // ring columns tx = -1 and tx = TW
+    if (tid < 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
         const int r = tid % SC_H, side = tid / SC_H;
-        const int tx = side ? VS_TW : -1;
-        const int gx = x0 + tx, gy = y0 - 1 + r;
-        int sc = 0;
-        if (gy >= cy_lo && gy <= cy_hi && gx >= cx_lo && gx <= cx_hi)
-            sc = fast_single(s_raw + (r + 3) * RAW_S + tx + VS_HALO, thr);
-        s_sc[r * SC_S + 4 + tx] = (uint16_t)sc;
+        const int wi = side ? VS_TW / 2 + 2 : 1;
+        const int gx = x0 + (side ? VS_TW : -1), gy = y0 - 1 + r;
+        if (gy >= cy_lo && gy <= cy_hi && gx >= cx_lo && gx <= cx_hi) {
+            const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
+            const uint32_t need = compass_need(rw[3 * (RAW_S / 2)], rw[-3 * (RAW_S / 2)], fsr16(rw[1], rw[2]), fsr16(rw[-2], rw[-1]),
+                                               rw[0], kbias) & (side ? 0x00008000u : 0x80000000u);
+            if (need) s_queue[atomicAdd(&s_nq, 1)] = (uint16_t)((r << 6) | wi);
+        }
+        ((uint32_t*)(s_sc + r * SC_S))[wi] = 0u;
+    }
+    __syncthreads();
+    // 3b. exact scores of the queued pairs: word wi of score row r <-> tile columns 2wi, 2wi+1
+    const int nqueue = s_nq;
+    for (int qi = tid; qi < nqueue; qi += 256) {
+        const int e = s_queue[qi], r = e >> 6, wi = e & 63;
+        const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
+        const int RW = RAW_S / 2;
+        uint32_t v[16];
+        {
+            const uint32_t m1 = rw[3 * RW - 1], z = rw[3 * RW], p1 = rw[3 * RW + 1];
+            v[0] = z; v[1] = fsr16(z, p1); v[15] = fsr16(m1, z);
+        }
+        {
+            const uint32_t m1 = rw[-3 * RW - 1], z = rw[-3 * RW], p1 = rw[-3 * RW + 1];
+            v[8] = z; v[7] = fsr16(z, p1); v[9] = fsr16(m1, z);
+        }
+        v[2] = rw[2 * RW + 1]; v[14] = rw[2 * RW - 1];
+        v[6] = rw[-2 * RW + 1]; v[10] = rw[-2 * RW - 1];
+        v[3] = fsr16(rw[RW + 1], rw[RW + 2]); v[13] = fsr16(rw[RW - 2], rw[RW - 1]);
+        v[5] = fsr16(rw[-RW + 1], rw[-RW + 2]); v[11] = fsr16(rw[-RW - 2], rw[-RW - 1]);
+        v[4] = fsr16(rw[1], rw[2]); v[12] = fsr16(rw[-2], rw[-1]);
+        uint32_t o = fast_pair(v, rw[0], kbias);
+        const int gx = x0 - VS_HALO + 2 * wi;
+        if (gx < cx_lo || gx > cx_hi) o &= 0xffff0000u;
+        if (gx + 1 < cx_lo || gx + 1 > cx_hi) o &= 0x0000ffffu;
+        ((uint32_t*)(s_sc + r * SC_S))[wi] = o;
     }
     __syncthreads();
 
