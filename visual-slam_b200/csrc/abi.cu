@@ -127,6 +127,10 @@ static int build_plan(const vslam_orb_params& prm, VsPlan& p, std::vector<uint32
         for (int axis = 0; axis < 2; ++axis) {
             const int n = axis == 0 ? L.w : L.h, src_n = axis == 0 ? p.lv[l - 1].w : p.lv[l - 1].h;
             const int tile = axis == 0 ? VS_TW : VS_TH, tiles = axis == 0 ? L.tiles_x : L.tiles_y;
+            // per-tile bounds (lo | hi << 16) of the staged parent region, read by the kernel
+            const int bnd_off = (int)tab.size();
+            tab.resize(tab.size() + tiles);
+            if (axis == 0) p.lv[l].bndx_off = bnd_off; else p.lv[l].bndy_off = bnd_off;
             const uint32_t* t = tab.data() + (axis == 0 ? L.tabx_off : L.taby_off);
             for (int k = 0; k < tiles; ++k) {
                 int lo = 0x7fffffff, hi = 0;
@@ -136,8 +140,9 @@ static int build_plan(const vslam_orb_params& prm, VsPlan& p, std::vector<uint32
                     hi = i0 > hi ? i0 : hi;
                 }
                 hi = hi + 1 < src_n - 1 ? hi + 1 : src_n - 1;
+                tab[bnd_off + k] = (uint32_t)lo | ((uint32_t)hi << 16);
                 if (axis == 0) {
-                    int wbytes = ((hi - (lo & ~3)) / 4 + 1) * 4;
+                    int wbytes = (int)align_up((size_t)(hi - (lo & ~15)) + 1, 16);   // TMA: box start and row length are multiples of 16 bytes
                     p.par_w = wbytes > p.par_w ? wbytes : p.par_w;
                 } else {
                     p.par_h = hi - lo + 1 > p.par_h ? hi - lo + 1 : p.par_h;

@@ -55,6 +55,7 @@ struct VsLevel {
     size_t stage_off;       // entry offset inside one frame's staging block
     int tiles_x, tiles_y;
     int tabx_off, taby_off; // offsets of this level's resize tables (from level l-1) in the table block
+    int bndx_off, bndy_off; // offsets of the per-tile parent-region bounds (lo | hi << 16) in the table block
 };
 
 // Device-side plan (kernel argument, passed by value through constant bank).

@@ -15,6 +15,8 @@
 //   4. applies the 7x7 sigma=2 float Gaussian in cv2's exact operation order (K7a) and
 //      stores the blurred level used by rBRIEF.
 // Level l therefore costs one read of level l-1 and two writes of level l in HBM.
+#include <cuda.h>
+
 #include "common.cuh"
 
 #define RAW_W (VS_TW + 2 * VS_HALO)   // 72 columns: x0-4 .. x0+67
@@ -24,7 +26,7 @@
 #define SC_S 72                       // score row stride; column index = tx + 4
 #define BL_ROWS (VS_TH + 6)
 #ifndef VS_LEVEL_CTAS
-#define VS_LEVEL_CTAS 4                // resident CTAs per SM the register budget is capped for (5 spills, no faster)
+#define VS_LEVEL_CTAS 5                // resident CTAs per SM the register budget is capped for (48 registers)
 #endif
 #define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
 
@@ -68,6 +70,14 @@ __device__ __forceinline__ uint32_t fast_pair(const uint32_t (&v)[16], uint32_t 
     uint32_t t2 = (Lo + kbias) - c;          // (Lo - c - thr) + 512
     uint32_t m = __vmaxu2(__vmaxu2(t1, t2), 0x02000200u);
     return m - 0x02000200u;                  // max(S - thr, 0) per lane
+}
+
+// plain shared-memory atomic add (inline PTX keeps the compiler from wrapping it in its own warp aggregation)
+__device__ __forceinline__ int smem_atomic_add(int* p, int v)
+{
+    int old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+    return old;
 }
 
 // Compass pre-test for a pixel pair: a, b, c, d = the circle points (0,+3), (0,-3), (+3,0), (-3,0), cen = centre.
@@ -192,11 +202,14 @@ __device__ __forceinline__ void blur_col_item(const float* p, uint32_t& out0, ui
     }
 }
 
+// L0 = true: level 0 (tile widened from the frame); false: levels >= 1 (tile resized from level - 1).
+// Two instantiations so that each gets its own register allocation and schedule.
+template <bool L0>
 __global__ void __launch_bounds__(256, VS_LEVEL_CTAS)
 vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* __restrict__ frames,
                 int fpitch, size_t fstride, uint8_t* __restrict__ pyr,
                 const uint32_t* __restrict__ tab, VsCand* __restrict__ cand,
-                int32_t* __restrict__ counters)
+                int32_t* __restrict__ counters, const __grid_constant__ CUtensorMap tmap, int use_tma)
 {
     // 8 elements of front padding: the networks of the ring column read one word left of row 0
     __shared__ __align__(16) uint16_t s_raw_store[RAW_H * RAW_S + 8];
@@ -208,7 +221,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __shared__ uint32_t s_hist[256];
     __shared__ VsCand s_list[LIST_CAP];
     __shared__ uint32_t s_tx[RAW_W], s_ty[RAW_H];
-    __shared__ int s_bnd[4];
+    __shared__ __align__(8) unsigned long long s_mbar;   // TMA completion barrier (levels >= 1)
     __shared__ int s_n, s_base;
     extern __shared__ __align__(16) uint8_t s_dyn[];   // parent region + horizontal pass (levels >= 1)
 
@@ -223,21 +236,30 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     if (tid == 0) { s_n = 0; s_nq = 0; }
 
     // ---- 1. raw tile (16-bit lanes) ------------------------------------------
-    if (level == 0) {
+    if (L0) {
         const uint8_t* src = frames + (size_t)b * fstride;
         const bool aligned = (((size_t)src | (size_t)fpitch) & 3) == 0;
         // thread = one 4-pixel word column x up to 3 rows; the loads are issued before any store
         const int wd = tid % (RAW_W / 4), rg = tid / (RAW_W / 4);        // 18 word columns x 14 row groups
+        const bool interior = x0 >= VS_HALO && x0 + VS_TW + VS_HALO <= W && y0 >= VS_HALO && y0 + VS_TH + VS_HALO <= H;
         if (rg < 14) {
-            const int gx = x0 - VS_HALO + 4 * wd;
-            const bool fast = aligned && gx >= 0 && gx + 3 < W;
             uint32_t u[3];
+            if (aligned && interior) {      // no reflection anywhere in the tile: three strided row loads
+                const uint8_t* p0 = src + (size_t)(y0 - VS_HALO + rg) * fpitch + (x0 - VS_HALO) + 4 * wd;
+                u[0] = __ldg((const uint32_t*)p0);
+                u[1] = __ldg((const uint32_t*)(p0 + (size_t)14 * fpitch));
+                u[2] = rg < RAW_H - 28 ? __ldg((const uint32_t*)(p0 + (size_t)28 * fpitch)) : 0u;
+            } else {
+                const int gx = x0 - VS_HALO + 4 * wd;
+                const bool fast = aligned && gx >= 0 && gx + 3 < W;
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const int r = rg + 14 * k;
-                if (r < RAW_H) {
-                    const uint8_t* row = src + (size_t)vs_reflect101(y0 - VS_HALO + r, H) * fpitch;
-                    u[k] = fast ? __ldg((const uint32_t*)(row + gx)) : load4_reflect(row, gx, W);
+                for (int k = 0; k < 3; ++k) {
+                    const int r = rg + 14 * k;
+                    u[k] = 0;
+                    if (r < RAW_H) {
+                        const uint8_t* row = src + (size_t)vs_reflect101(y0 - VS_HALO + r, H) * fpitch;
+                        u[k] = fast ? __ldg((const uint32_t*)(row + gx)) : load4_reflect(row, gx, W);
+                    }
                 }
             }
 #pragma unroll
@@ -256,29 +278,36 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         const bool aligned = (((size_t)src | (size_t)sp) & 3) == 0;
         const int sw = P.w, sh = P.h;
         const int PW = plan.par_w;
-        uint8_t* s_par = s_dyn;                                         // [par_h][par_w] parent pixels
-        uint16_t* s_h = (uint16_t*)(s_dyn + (size_t)plan.par_h * PW);   // [par_h][RAW_W] horizontal pass
-        // table entries of this tile's (reflected) columns / rows and the parent bounding box
-        const int wid = tid >> 5, lane = tid & 31;
-        if (wid < 2) {
-            const uint32_t* t = tab + (wid == 0 ? L.tabx_off : L.taby_off);
-            const int n = wid == 0 ? RAW_W : RAW_H, o0 = (wid == 0 ? x0 : y0) - VS_HALO, lim = wid == 0 ? W : H;
-            uint32_t* dst = wid == 0 ? s_tx : s_ty;
-            int lo = 0x7fffffff, hi = 0;
-            for (int c = lane; c < n; c += 32) {
-                uint32_t e = __ldg(t + vs_reflect101(o0 + c, lim));
-                dst[c] = e;
-                lo = min(lo, (int)(e & 0xffff));
-                hi = max(hi, (int)(e & 0xffff));
-            }
-            lo = __reduce_min_sync(0xffffffffu, lo);
-            hi = __reduce_max_sync(0xffffffffu, hi);
-            if (lane == 0) { s_bnd[2 * wid] = lo; s_bnd[2 * wid + 1] = min(hi + 1, (wid == 0 ? sw : sh) - 1); }
+        // dynamic smem: [par_h][par_w] parent pixels (128-byte aligned for TMA), then the horizontal pass
+        uint8_t* s_par = (uint8_t*)(((uintptr_t)s_dyn + 127) & ~(uintptr_t)127);
+        uint16_t* s_h = (uint16_t*)(s_par + (size_t)plan.par_h * PW);   // [par_h][RAW_W]
+        // bounding box of the parent pixels this tile reads (host-computed per tile column / row)
+        const uint32_t bx = __ldg(tab + L.bndx_off + blockIdx.x), by = __ldg(tab + L.bndy_off + blockIdx.y);
+        const int px_lo = (int)(bx & 0xffff), px_hi = (int)(bx >> 16), py0 = (int)(by & 0xffff);
+        const int nrows = (int)(by >> 16) - py0 + 1;
+        const int pxa = px_lo & ~15;                                    // parent column of s_par[.][0] (TMA needs 16-byte aligned starts)
+        if (use_tma && tid == 0) {
+            // one thread: arm the mbarrier with the box size and issue the 3-D tile load (x, y, frame);
+            // rows / columns of the box beyond the parent image are zero-filled and never read
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_par);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(PW * plan.par_h) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"(dst), "l"((uint64_t)&tmap), "r"(pxa), "r"(py0), "r"(b), "r"(bar) : "memory");
         }
-        __syncthreads();
-        const int pxa = s_bnd[0] & ~3, py0 = s_bnd[2];
-        const int nwords = (s_bnd[1] - pxa) / 4 + 1, nrows = s_bnd[3] - py0 + 1;
-        {   // stage the parent region: thread = one word column x every G-th row, 4 loads in flight
+        // table entries of this tile's (reflected) columns / rows
+        const int wid = tid >> 5, lane = tid & 31;
+        if (wid >= 6) {
+            const bool isx = wid == 6;
+            const uint32_t* t = tab + (isx ? L.tabx_off : L.taby_off);
+            const int n = isx ? RAW_W : RAW_H, o0 = (isx ? x0 : y0) - VS_HALO, lim = isx ? W : H;
+            uint32_t* dst = isx ? s_tx : s_ty;
+            for (int c = lane; c < n; c += 32) dst[c] = __ldg(t + vs_reflect101(o0 + c, lim));
+        }
+        if (!use_tma) {   // fallback (unaligned frames, very large scale factors): thread = one word column x every G-th row
+            const int nwords = (px_hi - pxa) / 4 + 1;
             const int PWW = PW >> 2, G = 256 / PWW;
             const int wd = tid % PWW, rg = tid / PWW;
             if (rg < G && wd < nwords) {
@@ -308,6 +337,14 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             }
         }
         __syncthreads();
+        if (use_tma) {    // wait for the tile (phase 0 of the single-use barrier)
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+            asm volatile(
+                "{\n .reg .pred p;\n"
+                "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+                " @p bra D%=;\n bra W%=;\n"
+                "D%=:\n}\n" ::"r"(bar) : "memory");
+        }
         // separable INTER_LINEAR_EXACT: thread = one column pair x every 7th row, so that the table
         // entries are loop invariant.  A column with i0 = sw-1 has weight 0 on its right neighbour,
         // whatever that byte is.
@@ -342,7 +379,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __syncthreads();
 
     // ---- 2. store the raw level -------------------------------------------
-    if (level > 0 && tid < VS_TH * 4) {
+    if (!L0 && tid < VS_TH * 4) {
         int row = tid >> 2, seg = tid & 3;
         int gx = x0 + seg * 16, gy = y0 + row;
         if (gx < L.pitch && gy < H) {
@@ -364,29 +401,40 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     // needs its second-largest compass value above c + thr or its second-smallest below c - thr.  Pixel
     // pairs that pass are queued; the full min/max networks (3b) then run on whole warps of queued pairs
     // only (a third to a half of the pairs on textured images) instead of on every pixel.
-    for (int i = tid; i < SC_H * (VS_TW / 4); i += 256) {
-        const int w = i & 15, r = i >> 4;
-        const int gy = y0 - 1 + r, gx = x0 + 4 * w;
-        uint32_t needA = 0, needB = 0;
-        if (gy >= cy_lo && gy <= cy_hi && gx + 3 >= cx_lo && gx <= cx_hi) {
-            const uint16_t* base = s_raw + (r + 3) * RAW_S + 4 * w;   // word 2 of this row = pixels 0,1
-            const uint2 up = *(const uint2*)(base + 3 * RAW_S + 4), dn = *(const uint2*)(base - 3 * RAW_S + 4);
-            const uint2* q = (const uint2*)base;
-            const uint2 a = q[0], m = q[1], e = q[2];
-            needA = compass_need(up.x, dn.x, fsr16(m.y, e.x), fsr16(a.x, a.y), m.x, kbias);
-            needB = compass_need(up.y, dn.y, fsr16(e.x, e.y), fsr16(a.y, m.x), m.y, kbias);
+    {
+        const int lane = tid & 31;
+        const int w = tid & 15;
+        uint32_t need[4];                 // pass k = score row (tid >> 4) + 16k; [2k] = pair A, [2k+1] = pair B
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int r = (tid >> 4) + 16 * k;
+            const int gy = y0 - 1 + r, gx = x0 + 4 * w;
+            need[2 * k] = need[2 * k + 1] = 0;
+            if (gy >= cy_lo && gy <= cy_hi && gx + 3 >= cx_lo && gx <= cx_hi) {
+                const uint16_t* base = s_raw + (r + 3) * RAW_S + 4 * w;   // word 2 of this row = pixels 0,1
+                const uint2 up = *(const uint2*)(base + 3 * RAW_S + 4), dn = *(const uint2*)(base - 3 * RAW_S + 4);
+                const uint2* q = (const uint2*)base;
+                const uint2 a = q[0], m = q[1], e = q[2];
+                need[2 * k] = compass_need(up.x, dn.x, fsr16(m.y, e.x), fsr16(a.x, a.y), m.x, kbias);
+                need[2 * k + 1] = compass_need(up.y, dn.y, fsr16(e.x, e.y), fsr16(a.y, m.x), m.y, kbias);
+            }
+            *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(0u, 0u);
         }
-        *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(0u, 0u);
-        // warp-aggregated push of (row, word) entries
-        const uint32_t mA = __ballot_sync(0xffffffffu, needA != 0), mB = __ballot_sync(0xffffffffu, needB != 0);
-        if (mA | mB) {
-            const int lane = tid & 31, nA = __popc(mA);
+        // one warp-aggregated push of (row, word) entries for the four masks
+        uint32_t mk[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) mk[j] = __ballot_sync(0xffffffffu, need[j] != 0);
+        const int c0 = __popc(mk[0]), c1 = __popc(mk[1]), c2 = __popc(mk[2]), c3 = __popc(mk[3]);
+        if (c0 + c1 + c2 + c3) {
             int basepos = 0;
-            if (lane == 0) basepos = atomicAdd(&s_nq, nA + __popc(mB));
+            if (lane == 0) basepos = smem_atomic_add(&s_nq, c0 + c1 + c2 + c3);
             basepos = __shfl_sync(0xffffffffu, basepos, 0);
             const uint32_t lt = (1u << lane) - 1u;
-            if (needA) s_queue[basepos + __popc(mA & lt)] = (uint16_t)((r << 6) | (2 * w + 2));
-            if (needB) s_queue[basepos + nA + __popc(mB & lt)] = (uint16_t)((r << 6) | (2 * w + 3));
+            const int r0 = tid >> 4;
+            if (need[0]) s_queue[basepos + __popc(mk[0] & lt)] = (uint16_t)((r0 << 6) | (2 * w + 2));
+            if (need[1]) s_queue[basepos + c0 + __popc(mk[1] & lt)] = (uint16_t)((r0 << 6) | (2 * w + 3));
+            if (need[2]) s_queue[basepos + c0 + c1 + __popc(mk[2] & lt)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 2));
+            if (need[3]) s_queue[basepos + c0 + c1 + c2 + __popc(mk[3] & lt)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 3));
         }
     }
     if (tid < 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
@@ -397,7 +445,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
             const uint32_t need = compass_need(rw[3 * (RAW_S / 2)], rw[-3 * (RAW_S / 2)], fsr16(rw[1], rw[2]), fsr16(rw[-2], rw[-1]),
                                                rw[0], kbias) & (side ? 0x00008000u : 0x80000000u);
-            if (need) s_queue[atomicAdd(&s_nq, 1)] = (uint16_t)((r << 6) | wi);
+            if (need) s_queue[smem_atomic_add(&s_nq, 1)] = (uint16_t)((r << 6) | wi);
         }
         ((uint32_t*)(s_sc + r * SC_S))[wi] = 0u;
     }
@@ -511,18 +559,54 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
 
 size_t vs_level_dyn_smem(const VsPlan& p)
 {
-    return (size_t)p.par_h * p.par_w + (size_t)p.par_h * RAW_W * sizeof(uint16_t);
+    return 128 + (size_t)p.par_h * p.par_w + (size_t)p.par_h * RAW_W * sizeof(uint16_t);
 }
 
 int vs_configure_level_smem(const VsPlan& p)
 {
     const size_t dyn = vs_level_dyn_smem(p);
-    if (dyn > 160 * 1024) {
+    if (dyn > 160 * 1024 || p.par_w > 1024) {
         vs_set_error("scale_factor too large for the level kernel's parent staging (%zu bytes)", dyn);
         return VSLAM_E_INVALID;
     }
-    VS_CUDA(cudaFuncSetAttribute(vs_level_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
     return VSLAM_OK;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point query (no link against libcuda)
+typedef CUresult (*vs_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                       const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                       CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static vs_encode_tiled_fn vs_encode_tiled()
+{
+    static vs_encode_tiled_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (vs_encode_tiled_fn)f;
+        cudaGetLastError();
+    }
+    return fn;
+}
+
+// Tensor map of a parent image stack uint8 [frames][h][pitch] with a (par_w, par_h, 1) box.  Returns false
+// when TMA cannot describe it (unaligned base / strides, box too large); the kernel then stages by hand.
+static bool vs_parent_tensor_map(CUtensorMap* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
+                                 int frames, const VsPlan& p)
+{
+    vs_encode_tiled_fn enc = vs_encode_tiled();
+    if (!enc || p.par_w > 256 || p.par_h > 256 || (p.par_w & 15)) return false;
+    if (((uintptr_t)base & 15) || (pitch & 15) || (frame_stride & 15)) return false;
+    const cuuint64_t gdim[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
+    const cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
+    const cuuint32_t box[3] = {(cuuint32_t)p.par_w, (cuuint32_t)p.par_h, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s)
@@ -534,11 +618,23 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
     for (int l = 0; l < p.n_levels; ++l) {
         const VsLevel& L = p.lv[l];
         if (L.w <= 0 || L.h <= 0) continue;
+        CUtensorMap tm;
+        memset(&tm, 0, sizeof(tm));
+        int use_tma = 0;
+        if (l == 1)
+            use_tma = vs_parent_tensor_map(&tm, d_frames, p.width, p.height, (size_t)pitch, (size_t)pitch * p.height, batch, p);
+        else if (l > 1)
+            use_tma = vs_parent_tensor_map(&tm, o->d_pyr + p.lv[l - 1].raw_off, p.lv[l - 1].w, p.lv[l - 1].h,
+                                           (size_t)p.lv[l - 1].pitch, p.pyr_frame_bytes, batch, p);
         dim3 grid(L.tiles_x, L.tiles_y, batch);
         vs_prof_mark(o, l, s);
         ++g_vs_launches;
-        vs_level_kernel<<<grid, 256, l > 0 ? dyn : 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height,
-                                                         o->d_pyr, o->d_tab, o->d_cand, o->d_counters);
+        if (l == 0)
+            vs_level_kernel<true><<<grid, 256, 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
+                                                       o->d_cand, o->d_counters, tm, 0);
+        else
+            vs_level_kernel<false><<<grid, 256, dyn, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
+                                                          o->d_cand, o->d_counters, tm, use_tma);
     }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
