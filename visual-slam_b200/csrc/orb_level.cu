@@ -279,7 +279,8 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         const int sw = P.w, sh = P.h;
         const int PW = plan.par_w;
         // dynamic smem: [par_h][par_w] parent pixels (128-byte aligned for TMA), then the horizontal pass
-        uint8_t* s_par = (uint8_t*)(((uintptr_t)s_dyn + 127) & ~(uintptr_t)127);
+        // (offset arithmetic on s_dyn, not on a generic address, so that the accesses stay LDS/STS)
+        uint8_t* s_par = s_dyn + ((128u - ((uint32_t)__cvta_generic_to_shared(s_dyn) & 127u)) & 127u);
         uint16_t* s_h = (uint16_t*)(s_par + (size_t)plan.par_h * PW);   // [par_h][RAW_W]
         // bounding box of the parent pixels this tile reads (host-computed per tile column / row)
         const uint32_t bx = __ldg(tab + L.bndx_off + blockIdx.x), by = __ldg(tab + L.bndy_off + blockIdx.y);

@@ -257,9 +257,8 @@ __device__ const float4 g_patf_t[256] = {
 
 // Copy a rows x (4*words)-byte window starting at the 4-byte aligned column xs of row ys into shared
 // memory.  Lane = (row group, word): the row pointer advances by a fixed stride, no per-load index math.
-template <int ROWS, int WORDS>
-__device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, int pitch, int xs, int ys, int lane,
-                                             bool aligned)
+template <int ROWS, int WORDS, bool ALIGNED>
+__device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, int pitch, int xs, int ys, int lane)
 {
     constexpr int RG = 32 / WORDS;                  // rows per pass
     const int r0 = lane / WORDS, cw = lane - r0 * WORDS;
@@ -267,16 +266,19 @@ __device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, i
     const uint8_t* src = img + (size_t)(ys + r0) * pitch + xs + 4 * cw;
     uint32_t* dst = (uint32_t*)win + r0 * WORDS + cw;
     const size_t step = (size_t)pitch * RG;
+    uint32_t v[(ROWS + RG - 1) / RG];
 #pragma unroll
-    for (int r = 0; r < ROWS; r += RG) {
-        if (r + r0 < ROWS) {
-            uint32_t v;
-            if (aligned) v = __ldg((const uint32_t*)src);
-            else v = (uint32_t)__ldg(src) | ((uint32_t)__ldg(src + 1) << 8) | ((uint32_t)__ldg(src + 2) << 16) | ((uint32_t)__ldg(src + 3) << 24);
-            dst[r * WORDS] = v;
+    for (int k = 0; k < (ROWS + RG - 1) / RG; ++k) {            // all loads first, then the stores
+        v[k] = 0;
+        if (k * RG + r0 < ROWS) {
+            if (ALIGNED) v[k] = __ldg((const uint32_t*)src);
+            else v[k] = (uint32_t)__ldg(src) | ((uint32_t)__ldg(src + 1) << 8) | ((uint32_t)__ldg(src + 2) << 16) | ((uint32_t)__ldg(src + 3) << 24);
         }
         src += step;
     }
+#pragma unroll
+    for (int k = 0; k < (ROWS + RG - 1) / RG; ++k)
+        if (k * RG + r0 < ROWS) dst[k * RG * WORDS] = v[k];
 }
 
 // One warp per keypoint, VS_DESC_PER_WARP keypoints in turn.  Keypoints are at least 31 px inside
@@ -293,27 +295,35 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
     __shared__ __align__(16) uint8_t s_raw[8][IC_WIN * IC_WIN_S];
     const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int32_t* ctr = counters + (size_t)b * plan.n_levels * VS_CTR_STRIDE;
-    // start of each level's keypoints in the frame's output rows
-    int nfin[VS_MAX_LEVELS], total = 0;
+    // start of each level's keypoints in the frame's output rows (prefix sums of the final counts)
+    __shared__ int s_start[VS_MAX_LEVELS + 1];
+    if (threadIdx.x < 32) {
+        const int l = threadIdx.x;
+        int n = l < plan.n_levels ? ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL] : 0, incl = n;
 #pragma unroll
-    for (int l = 0; l < VS_MAX_LEVELS; ++l) {
-        nfin[l] = l < plan.n_levels ? ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL] : 0;
-        total += nfin[l];
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (l >= o) incl += t;
+        }
+        if (l <= VS_MAX_LEVELS) s_start[l] = incl - n;          // s_start[n_levels..] = total
     }
+    __syncthreads();
+    const int total = s_start[plan.n_levels];
     if (blockIdx.x == 0 && threadIdx.x == 0) count_out[b] = total;
+    const bool frames_aligned = ((((size_t)frames) | (size_t)fpitch | fstride) & 3) == 0;
     const uint8_t* fp = pyr + (size_t)b * plan.pyr_frame_bytes;
     uint8_t* wb = s_blur[wid];
     uint8_t* wr = s_raw[wid];
     const int u = lane - VS_HALF_PATCH;              // lanes 0..30 <-> columns -15..15 of the disc
     const int vmax = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;   // the disc is symmetric: |v| <= umax[|u|]
 
+    int level = 0;
     for (int k = 0; k < VS_DESC_PER_WARP; ++k) {
         const int i = (blockIdx.x * 8 + wid) * VS_DESC_PER_WARP + k;
         if (i >= total || i >= plan.kp_cap) break;
-        int level = 0, j = i;
-#pragma unroll
-        for (int l = 0; l < VS_MAX_LEVELS - 1; ++l)
-            if (level == l && j >= nfin[l]) { j -= nfin[l]; level = l + 1; }
+        while (level + 1 < plan.n_levels && i >= s_start[level + 1]) ++level;   // warp-uniform, monotone in k
+        const int j = i - s_start[level];
+        const bool raw_aligned = level > 0 || frames_aligned;
         const VsLevel& L = plan.lv[level];
         const VsCand c = stage[(size_t)b * plan.stage_frame_entries + L.stage_off + j];
         const uint8_t* raw;
@@ -324,8 +334,8 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
         const int x0 = c.x, y0 = c.y;
         const int rxs = (x0 - VS_HALF_PATCH) & ~3;
         __syncwarp();
-        stage_window<IC_WIN, IC_WIN_S / 4>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane,
-                                            (((size_t)raw | (size_t)rpitch) & 3) == 0);
+        if (raw_aligned) stage_window<IC_WIN, IC_WIN_S / 4, true>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane);
+        else stage_window<IC_WIN, IC_WIN_S / 4, false>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane);
         __syncwarp();
         int m10 = 0, m01 = 0;
         {
@@ -362,7 +372,7 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
         sincos((double)rad, &sd, &cd);
         const float ca = (float)cd, sa = (float)sd;
         const int xs = (cx - DESC_R) & ~3;
-        stage_window<DESC_WIN, DESC_WIN_S / 4>(wb, fp + L.blur_off, L.pitch, xs, cy - DESC_R, lane, true);
+        stage_window<DESC_WIN, DESC_WIN_S / 4, true>(wb, fp + L.blur_off, L.pitch, xs, cy - DESC_R, lane);
         __syncwarp();
         // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
         const float magic = 12582912.0f;
