@@ -41,17 +41,31 @@ __device__ __forceinline__ int suffix_sum_256(int val, int* s_w)
 }
 
 // Harris response of cv2.ORB (7x7 block of 3x3 Sobel, k = 0.04), SURVEY.md 8(a) K4.
+// ALIGNED: rows are 4-byte aligned, so the 9 bytes of a row come from three aligned 32-bit loads
+// (funnel-shifted by the column's byte offset) instead of nine byte loads -- the kernel is bound by
+// load latency, not arithmetic.
+template <bool ALIGNED>
 __device__ __forceinline__ float harris_response(const uint8_t* img, int pitch, int x0, int y0)
 {
     int a = 0, b = 0, c = 0;
     int dxm[7], sxm[7], dxc[7], sxc[7];
+    const int xa = (x0 - 4) & ~3, sh = ((x0 - 4) & 3) * 8;
     // rows y0-4 .. y0+4; Sobel at row r uses rows r-1, r, r+1
 #pragma unroll
     for (int r = 0; r < 9; ++r) {
-        const uint8_t* p = img + (size_t)(y0 - 4 + r) * pitch + (x0 - 4);
         int v[9];
+        if (ALIGNED) {
+            const uint32_t* p = (const uint32_t*)(img + (size_t)(y0 - 4 + r) * pitch + xa);
+            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+            const uint32_t q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh), q2 = w2 >> sh;
+            v[0] = q0 & 0xff; v[1] = (q0 >> 8) & 0xff; v[2] = (q0 >> 16) & 0xff; v[3] = q0 >> 24;
+            v[4] = q1 & 0xff; v[5] = (q1 >> 8) & 0xff; v[6] = (q1 >> 16) & 0xff; v[7] = q1 >> 24;
+            v[8] = q2 & 0xff;
+        } else {
+            const uint8_t* p = img + (size_t)(y0 - 4 + r) * pitch + (x0 - 4);
 #pragma unroll
-        for (int j = 0; j < 9; ++j) v[j] = __ldg(p + j);
+            for (int j = 0; j < 9; ++j) v[j] = __ldg(p + j);
+        }
         int dxn[7], sxn[7];
 #pragma unroll
         for (int j = 0; j < 7; ++j) {
@@ -114,12 +128,13 @@ vs_harris_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict_
     if (level == 0) { img = frames + (size_t)b * fstride; pitch = fpitch; }
     else { img = pyr + (size_t)b * plan.pyr_frame_bytes + L.raw_off; pitch = L.pitch; }
     VsCand* cl = cand + (size_t)b * plan.cand_frame_entries + L.cand_off;
+    const bool aligned = (((size_t)img | (size_t)pitch) & 3) == 0;
     int nsurv = 0;
     for (int i = blockIdx.x * 256 + tid; i < ncand; i += VS_HARRIS_CTAS * 256) {
         VsCand c = cl[i];
         uint32_t key = 0;
         if ((int)c.v >= thr) {
-            key = f2key(harris_response(img, pitch, c.x, c.y));
+            key = f2key(aligned ? harris_response<true>(img, pitch, c.x, c.y) : harris_response<false>(img, pitch, c.x, c.y));
             if (key == 0) key = 1;
             ++nsurv;
         }
