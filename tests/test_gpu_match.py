@@ -120,3 +120,26 @@ def test_frontend_host_chunked_pipeline_equals_unfused(oracle):
     assert np.array_equal(cnt2, cnt[:3]) and np.array_equal(mc2, mc[:2])
     assert np.array_equal(match2[0][:mc2[0]], match[0][:mc[0]])
     h.close(); h1.close()
+
+
+def test_knn2_mma_sync_engine_still_exact(tmp_path):
+    """The default kNN-2 engine is the tcgen05 kernel; the mma.sync int8 kernel stays selectable
+    (VSLAM_KNN=imma, read once per process) and must give the same bit-exact answers."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from orbslam2 import _native\n"
+        "from oracle import oracle as O\n"
+        "for nq, nt in ((1, 1), (257, 63), (2000, 2000), (300, 5000)):\n"
+        "    q = np.random.default_rng(nq).integers(0, 256, (nq, 32), dtype=np.uint8)\n"
+        "    t = np.random.default_rng(nt + 1).integers(0, 256, (nt, 32), dtype=np.uint8)\n"
+        "    i, d = _native.bf_knn2_host(q, t); ri, rd = O.bf_knn2(q, t)\n"
+        "    assert np.array_equal(i, ri) and np.array_equal(d, rd), (nq, nt)\n"
+        "print('ok')\n" % (os.path.join(root, "visual-slam_b200"), root))
+    env = dict(os.environ, VSLAM_KNN="imma")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]

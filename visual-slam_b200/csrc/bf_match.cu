@@ -10,7 +10,13 @@
 // 8 XOR + 8 POPC + adds and a predicated two-deep insert.  The train range can be split
 // over blockIdx.y (partials merged in ascending split order, which preserves the tie
 // rule); blockIdx.z runs over descriptor-set pairs (consecutive frames of a batch).
+#include <stdlib.h>
+
 #include "common.cuh"
+
+#ifndef VS_KNN_DEFAULT_TC5
+#define VS_KNN_DEFAULT_TC5 1
+#endif
 
 #define BF_THREADS 128
 #define BF_TILE 128   // train descriptors per shared-memory tile (4 KiB)
@@ -298,6 +304,24 @@ __global__ void vs_knn2_merge_kernel(const int4* __restrict__ partial, int nq_ma
     out_dist[o + 1] = best.i2 >= 0 ? best.d2 : -1;
 }
 
+int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt, long t_stride,
+                       const int32_t* d_nq, const int32_t* d_nt, int pairs, int nsplit, int4* partial,
+                       int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
+
+// kNN-2 engine for nt < 65536: 1 = tcgen05 kind::i8 (bf_match_tc5.cu), 0 = mma.sync int8 (above).
+// VSLAM_KNN=imma|tc5 overrides the default.
+static int knn_use_tc5()
+{
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("VSLAM_KNN");
+        mode = VS_KNN_DEFAULT_TC5;
+        if (e && !strcmp(e, "imma")) mode = 0;
+        if (e && !strcmp(e, "tc5")) mode = 1;
+    }
+    return mode;
+}
+
 static int4* g_partial = nullptr;
 static size_t g_partial_bytes = 0;
 
@@ -308,7 +332,8 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     if (pairs <= 0 || nq <= 0) return VSLAM_OK;
     const bool mma = nt < 65536;   // the tensor-core kernel packs the train index into 16 bits
     const int qtiles = mma ? (nq + KT_Q - 1) / KT_Q : (nq + BF_THREADS - 1) / BF_THREADS;
-    const int ttiles = mma ? (nt + KT_T - 1) / KT_T : (nt + BF_TILE - 1) / BF_TILE;
+    const bool tc5 = mma && knn_use_tc5();
+    const int ttiles = tc5 ? (nt + 127) / 128 : mma ? (nt + KT_T - 1) / KT_T : (nt + BF_TILE - 1) / BF_TILE;
     // split the train range only when the grid would not fill the 148 SMs a few times over
     int nsplit = 1;
     const long want = 148L * 8;
@@ -327,7 +352,10 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     }
     vs_prof_mark(prof, VS_PROF_KNN2, s);
     ++g_vs_launches;
-    if (mma)
+    if (tc5) {
+        int rc = vs_knn2_tc5_launch(d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, pairs, nsplit, g_partial, d_idx, d_dist, s);
+        if (rc) return rc;
+    } else if (mma)
         vs_knn2_mma_kernel<<<dim3(qtiles, nsplit, pairs), 256, 0, s>>>(
             d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, g_partial, d_idx, d_dist);
     else

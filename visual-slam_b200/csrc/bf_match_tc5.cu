@@ -1,0 +1,238 @@
+// bf_match_tc5.cu -- brute-force Hamming kNN-2 on the 5th-generation tensor cores (tcgen05, kind::i8).
+//
+// Same contract as vs_knn2_kernel / vs_knn2_mma_kernel in bf_match.cu (cv2.BFMatcher(NORM_HAMMING).knnMatch
+// k=2, matcher.py:70), same arithmetic as the mma.sync variant: descriptor bits are
+// expanded to 0/1 bytes, dot(a, b) = popc(a & b), hamming = popc(a) + popc(b) - 2 dot, top-2 per query as
+// packed signed keys ((popc(b) - 2 dot) << 16 | train index), popc(a) added at the end.
+//
+// One CTA = 256 query rows = two M=128 UMMA tiles; train descriptors stream in tiles of N=128.
+//   * operands live in shared memory in the canonical K-major no-swizzle UMMA layout (8-row x 16-byte
+//     core matrices; LBO = 128 B between the K halves, SBO = 2048 B between 8-row groups); the bit
+//     expansion writes that layout directly (the k order of a dot product is free, so k = bit index),
+//   * one thread issues 2 x 8 tcgen05.mma (M128 N128 K32, u8 x u8 -> s32) per train tile into one of two
+//     256-column TMEM buffers and commits to an mbarrier,
+//   * all 8 warps expand the next train tile while the tensor core works, then read the finished tile
+//     back with tcgen05.ld 32x32b (thread = TMEM lane = query row, so the top-2 state is private to a
+//     thread and needs no shuffle merge).
+#include "common.cuh"
+
+#define T5_ROWS 256          // query rows per CTA
+#define T5_N 128             // train descriptors per tile
+#define T5_OPER_BYTES 32768  // one 128-row operand tile: 16 groups x 2048 B
+#define T5_INVALID 0x7fff0000
+
+__device__ __forceinline__ uint32_t t5_expand(uint32_t n) { return (n * 0x00204081u) & 0x01010101u; }
+
+// 32 descriptor bits -> 32 bytes of 0/1 = the two 16-byte core-matrix rows of one K=32 step
+__device__ __forceinline__ void t5_expand_word(uint32_t w, uint4& lo, uint4& hi)
+{
+    lo = make_uint4(t5_expand(w & 15u), t5_expand((w >> 4) & 15u), t5_expand((w >> 8) & 15u), t5_expand((w >> 12) & 15u));
+    hi = make_uint4(t5_expand((w >> 16) & 15u), t5_expand((w >> 20) & 15u), t5_expand((w >> 24) & 15u), t5_expand(w >> 28));
+}
+
+// (row, half) of a 128-row operand tile: expand words 4*half .. 4*half+3 of the descriptor
+__device__ __forceinline__ void t5_store_half(uint8_t* tile, int row, int half, const uint4& d)
+{
+    uint8_t* base = tile + (row >> 3) * 2048 + (row & 7) * 16 + half * 1024;   // k-step s = 4*half + j at + j*256
+    const uint32_t w[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        uint4 lo, hi;
+        t5_expand_word(w[j], lo, hi);
+        *(uint4*)(base + j * 256) = lo;
+        *(uint4*)(base + j * 256 + 128) = hi;
+    }
+}
+
+__device__ __forceinline__ uint64_t t5_smem_desc(uint32_t saddr)
+{
+    // start address, LBO = 128 B, SBO = 2048 B (all >> 4), descriptor version 1 (sm_100), no swizzle
+    return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)(128u >> 4) << 16) | ((uint64_t)(2048u >> 4) << 32) | (1ull << 46);
+}
+
+__device__ __forceinline__ void t5_top2(int& k1, int& k2, int x, int y)
+{
+    const int lo = min(x, y), hi = max(x, y);
+    const int n2 = __vimin3_s32(max(k1, lo), k2, hi);
+    k1 = min(k1, lo);
+    k2 = n2;
+}
+
+__global__ void __launch_bounds__(256, 1)
+vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
+                   const uint8_t* __restrict__ train, int nt_max, long t_stride,
+                   const int32_t* __restrict__ d_nq, const int32_t* __restrict__ d_nt,
+                   int nsplit, int4* __restrict__ partial, int32_t* __restrict__ out_idx,
+                   int32_t* __restrict__ out_dist)
+{
+    extern __shared__ __align__(128) uint8_t t5_smem[];
+    __shared__ __align__(8) unsigned long long s_bar[2];
+    __shared__ __align__(16) int32_t s_c[2][T5_N];
+    __shared__ uint32_t s_tmem;
+    const int pair = blockIdx.z, split = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nq = d_nq ? min(d_nq[pair], nq_max) : nq_max;
+    const int nt = d_nt ? min(d_nt[pair], nt_max) : nt_max;
+    const int q0 = blockIdx.x * T5_ROWS;
+    const int myrow = q0 + (wid >> 2) * 128 + (wid & 3) * 32 + lane;     // TMEM lane (wid & 3) * 32 + lane of M-tile wid >> 2
+    if (q0 >= nq) {
+        const int q = q0 + tid;
+        if (q < nq_max && split == 0) {
+            size_t o = ((size_t)pair * nq_max + q) * 2;
+            out_idx[o] = -1; out_idx[o + 1] = -1; out_dist[o] = -1; out_dist[o + 1] = -1;
+        }
+        return;
+    }
+    uint8_t* sm = t5_smem + ((128u - ((uint32_t)__cvta_generic_to_shared(t5_smem) & 127u)) & 127u);
+    uint8_t* sA = sm;                         // 2 x 32 KB: query rows 0..127, 128..255
+    uint8_t* sB = sm + 2 * T5_OPER_BYTES;     // 2 x 32 KB: train tile double buffer
+    const uint32_t sA_u = (uint32_t)__cvta_generic_to_shared(sA), sB_u = (uint32_t)__cvta_generic_to_shared(sB);
+    const uint32_t bar_u = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
+
+    // ---- TMEM (all 512 columns: two buffers of 2 x 128), barriers
+    if (wid == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_tmem)));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_u + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // ---- query rows -> A operand, popc(a) of this thread's row
+    const uint8_t* qbase = query + (size_t)pair * q_stride * 32;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const int item = tid + 256 * it, row = item >> 1, half = item & 1;
+        const uint4 d = __ldg((const uint4*)(qbase + (size_t)min(q0 + row, nq - 1) * 32) + half);
+        t5_store_half(sA + (row >> 7) * T5_OPER_BYTES, row & 127, half, d);
+    }
+    int pa;
+    {
+        const uint4* qp = (const uint4*)(qbase + (size_t)min(myrow, nq - 1) * 32);
+        const uint4 x = __ldg(qp), y = __ldg(qp + 1);
+        pa = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
+    }
+    const uint8_t* tp = train + (size_t)pair * t_stride * 32;
+    const int tiles = (nt + T5_N - 1) / T5_N;
+    const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
+
+    auto expand_tile = [&](int tile, int buf) {      // thread = (train row, half); the row's two threads share popc(b)
+        const int row = tid >> 1, half = tid & 1, d_idx = tile * T5_N + row;
+        uint4 d = make_uint4(0u, 0u, 0u, 0u);
+        if (d_idx < nt) d = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + half);
+        t5_store_half(sB + buf * T5_OPER_BYTES, row, half, d);
+        int pb = __popc(d.x) + __popc(d.y) + __popc(d.z) + __popc(d.w);
+        pb += __shfl_xor_sync(0xffffffffu, pb, 1);
+        if (half == 0) s_c[buf][row] = d_idx < nt ? ((pb << 16) | d_idx) : (T5_INVALID | (d_idx & 0xffff));
+    };
+    auto issue_tile = [&](int buf) {                 // one thread: 2 M-tiles x 8 K-steps, then commit to the buffer's barrier
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t idesc = (2u << 4) | ((uint32_t)(T5_N >> 3) << 17) | ((128u >> 4) << 24);   // s32 accum, u8 x u8, K-major both
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            const uint32_t tacc = s_tmem + buf * 256 + m * 128;
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+                const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
+                const uint64_t db = t5_smem_desc(sB_u + buf * T5_OPER_BYTES + s * 256);
+                const uint32_t accumulate = s > 0;
+                asm volatile(
+                    "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                    " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
+                    ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_u + 8 * buf) : "memory");
+    };
+
+    int k1 = 0x7fffffff, k2 = 0x7fffffff;
+    if (t_begin < t_end) expand_tile(t_begin, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = s_tmem;
+    if (tid == 0 && t_begin < t_end) issue_tile(0);
+
+    for (int tile = t_begin; tile < t_end; ++tile) {
+        const int i = tile - t_begin, buf = i & 1;
+        if (tile + 1 < t_end) {
+            expand_tile(tile + 1, buf ^ 1);          // its previous reader (MMA of tile - 1) completed before the last epilogue
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        __syncthreads();
+        if (tid == 0 && tile + 1 < t_end) issue_tile(buf ^ 1);
+        // wait for this tile's accumulators
+        {
+            const uint32_t parity = (uint32_t)(i >> 1) & 1u;
+            asm volatile(
+                "{\n .reg .pred p;\n"
+                "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                " @p bra D%=;\n bra W%=;\n"
+                "D%=:\n}\n" ::"r"(bar_u + 8 * buf), "r"(parity) : "memory");
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + (wid >> 2) * 128;
+#pragma unroll 1
+        for (int c0 = 0; c0 < T5_N; c0 += 32) {
+            uint32_t v[32];
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                  "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+                  "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+                  "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr + c0));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const int4 cc = *(const int4*)&s_c[buf][c0 + j];
+                t5_top2(k1, k2, (int)v[j] * -131072 + cc.x, (int)v[j + 1] * -131072 + cc.y);
+                t5_top2(k1, k2, (int)v[j + 2] * -131072 + cc.z, (int)v[j + 3] * -131072 + cc.w);
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
+
+    if (myrow < nq_max) {
+        const bool v1 = k1 < T5_INVALID, v2 = k2 < T5_INVALID;
+        int d1 = v1 ? (k1 >> 16) + pa : -1, i1 = v1 ? (k1 & 0xffff) : -1;
+        int d2 = v2 ? (k2 >> 16) + pa : -1, i2 = v2 ? (k2 & 0xffff) : -1;
+        if (myrow >= nq) {
+            if (split != 0) return;
+            d1 = d2 = i1 = i2 = -1;
+        }
+        if (nsplit == 1 || myrow >= nq) {
+            size_t o = ((size_t)pair * nq_max + myrow) * 2;
+            out_idx[o] = i1; out_idx[o + 1] = i2; out_dist[o] = d1; out_dist[o + 1] = d2;
+        } else {
+            partial[((size_t)pair * nsplit + split) * nq_max + myrow] = make_int4(d1, i1, d2, i2);
+        }
+    }
+}
+
+#define T5_DYN_SMEM (4 * T5_OPER_BYTES + 128)
+
+int vs_knn2_tc5_configure()
+{
+    static int done = 0;
+    if (!done) {
+        VS_CUDA(cudaFuncSetAttribute(vs_knn2_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T5_DYN_SMEM));
+        done = 1;
+    }
+    return VSLAM_OK;
+}
+
+int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt, long t_stride,
+                       const int32_t* d_nq, const int32_t* d_nt, int pairs, int nsplit, int4* partial,
+                       int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
+{
+    int rc = vs_knn2_tc5_configure();
+    if (rc) return rc;
+    vs_knn2_tc5_kernel<<<dim3((nq + T5_ROWS - 1) / T5_ROWS, nsplit, pairs), 256, T5_DYN_SMEM, s>>>(
+        d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, partial, d_idx, d_dist);
+    return VSLAM_OK;
+}
