@@ -58,6 +58,32 @@ __device__ __forceinline__ void t5_top2(int& k1, int& k2, int x, int y)
     k2 = n2;
 }
 
+// 32 consecutive accumulator columns of this thread's TMEM lane (asynchronous until tcgen05.wait::ld)
+__device__ __forceinline__ void t5_tmem_ld32(uint32_t (&v)[32], uint32_t taddr)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+}
+
+// fold 32 dot products (columns with key constants c[0..31]) into the four top-2 chains
+__device__ __forceinline__ void t5_reduce32(const uint32_t (&v)[32], const int32_t* c, int (&k1)[4], int (&k2)[4])
+{
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        const int4 cc = *(const int4*)(c + j), cd = *(const int4*)(c + j + 4);
+        t5_top2(k1[0], k2[0], (int)v[j] * -131072 + cc.x, (int)v[j + 1] * -131072 + cc.y);
+        t5_top2(k1[1], k2[1], (int)v[j + 2] * -131072 + cc.z, (int)v[j + 3] * -131072 + cc.w);
+        t5_top2(k1[2], k2[2], (int)v[j + 4] * -131072 + cd.x, (int)v[j + 5] * -131072 + cd.y);
+        t5_top2(k1[3], k2[3], (int)v[j + 6] * -131072 + cd.z, (int)v[j + 7] * -131072 + cd.w);
+    }
+}
+
 __global__ void __launch_bounds__(256, 1)
 vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
                    const uint8_t* __restrict__ train, int nt_max, long t_stride,
@@ -102,7 +128,7 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     const uint8_t* qbase = query + (size_t)pair * q_stride * 32;
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
-        const int item = tid + 256 * it, row = item >> 1, half = item & 1;
+        const int item = tid + 256 * it, row = item & 255, half = item >> 8;
         const uint4 d = __ldg((const uint4*)(qbase + (size_t)min(q0 + row, nq - 1) * 32) + half);
         t5_store_half(sA + (row >> 7) * T5_OPER_BYTES, row & 127, half, d);
     }
@@ -116,14 +142,20 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     const int tiles = (nt + T5_N - 1) / T5_N;
     const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
 
-    auto expand_tile = [&](int tile, int buf) {      // thread = (train row, half); the row's two threads share popc(b)
-        const int row = tid >> 1, half = tid & 1, d_idx = tile * T5_N + row;
-        uint4 d = make_uint4(0u, 0u, 0u, 0u);
-        if (d_idx < nt) d = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + half);
+    // thread = (train row, half) with consecutive lanes on consecutive rows: a quarter-warp's 128-bit stores
+    // cover one 128-byte core-matrix column (conflict-free); half 0 also reads the other half for popc(b)
+    auto expand_tile = [&](int tile, int buf) {
+        const int row = tid & 127, half = tid >> 7, d_idx = tile * T5_N + row;
+        uint4 d = make_uint4(0u, 0u, 0u, 0u), e = d;
+        if (d_idx < nt) {
+            d = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + half);
+            if (half == 0) e = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + 1);
+        }
         t5_store_half(sB + buf * T5_OPER_BYTES, row, half, d);
-        int pb = __popc(d.x) + __popc(d.y) + __popc(d.z) + __popc(d.w);
-        pb += __shfl_xor_sync(0xffffffffu, pb, 1);
-        if (half == 0) s_c[buf][row] = d_idx < nt ? ((pb << 16) | d_idx) : (T5_INVALID | (d_idx & 0xffff));
+        if (half == 0) {
+            const int pb = __popc(d.x) + __popc(d.y) + __popc(d.z) + __popc(d.w) + __popc(e.x) + __popc(e.y) + __popc(e.z) + __popc(e.w);
+            s_c[buf][row] = d_idx < nt ? ((pb << 16) | d_idx) : (T5_INVALID | (d_idx & 0xffff));
+        }
     };
     auto issue_tile = [&](int buf) {                 // one thread: 2 M-tiles x 8 K-steps, then commit to the buffer's barrier
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -145,7 +177,10 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_u + 8 * buf) : "memory");
     };
 
-    int k1 = 0x7fffffff, k2 = 0x7fffffff;
+    // four independent top-2 chains per thread (the update is a 3-deep dependent chain), merged at the end
+    int k1[4], k2[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { k1[c] = 0x7fffffff; k2[c] = 0x7fffffff; }
     if (t_begin < t_end) expand_tile(t_begin, 0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -173,34 +208,37 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + (wid >> 2) * 128;
-#pragma unroll 1
-        for (int c0 = 0; c0 < T5_N; c0 += 32) {
-            uint32_t v[32];
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-                  "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-                  "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-                  "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                : "r"(taddr + c0));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                const int4 cc = *(const int4*)&s_c[buf][c0 + j];
-                t5_top2(k1, k2, (int)v[j] * -131072 + cc.x, (int)v[j + 1] * -131072 + cc.y);
-                t5_top2(k1, k2, (int)v[j + 2] * -131072 + cc.z, (int)v[j + 3] * -131072 + cc.w);
-            }
-        }
+        // four 32-column chunks, the TMEM load of chunk c+1 in flight while chunk c is reduced
+        uint32_t va[32], vb[32];
+        t5_tmem_ld32(va, taddr);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        t5_tmem_ld32(vb, taddr + 32);
+        t5_reduce32(va, &s_c[buf][0], k1, k2);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        t5_tmem_ld32(va, taddr + 64);
+        t5_reduce32(vb, &s_c[buf][32], k1, k2);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        t5_tmem_ld32(vb, taddr + 96);
+        t5_reduce32(va, &s_c[buf][64], k1, k2);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        t5_reduce32(vb, &s_c[buf][96], k1, k2);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
     if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
 
     if (myrow < nq_max) {
-        const bool v1 = k1 < T5_INVALID, v2 = k2 < T5_INVALID;
-        int d1 = v1 ? (k1 >> 16) + pa : -1, i1 = v1 ? (k1 & 0xffff) : -1;
-        int d2 = v2 ? (k2 >> 16) + pa : -1, i2 = v2 ? (k2 & 0xffff) : -1;
+        // merge the four chains: two sorted pairs -> the two smallest of the four keys
+#pragma unroll
+        for (int c = 1; c < 4; ++c) {
+            const int n2 = __vimin3_s32(max(k1[0], k1[c]), k2[0], k2[c]);
+            k1[0] = min(k1[0], k1[c]);
+            k2[0] = n2;
+        }
+        const int kk1 = k1[0], kk2 = k2[0];
+        const bool v1 = kk1 < T5_INVALID, v2 = kk2 < T5_INVALID;
+        int d1 = v1 ? (kk1 >> 16) + pa : -1, i1 = v1 ? (kk1 & 0xffff) : -1;
+        int d2 = v2 ? (kk2 >> 16) + pa : -1, i2 = v2 ? (kk2 & 0xffff) : -1;
         if (myrow >= nq) {
             if (split != 0) return;
             d1 = d2 = i1 = i2 = -1;
