@@ -17,6 +17,7 @@
 #include "common.cuh"
 
 #define T5_ROWS 256          // query rows per CTA
+#define T5_THREADS 512       // 16 warps: warps w and w + 8 read the same TMEM lanes, one column half each
 #define T5_N 128             // train descriptors per tile
 #define T5_OPER_BYTES 32768  // one 128-row operand tile: 16 groups x 2048 B
 #define T5_INVALID 0x7fff0000
@@ -42,6 +43,17 @@ __device__ __forceinline__ void t5_store_half(uint8_t* tile, int row, int half, 
         *(uint4*)(base + j * 256) = lo;
         *(uint4*)(base + j * 256 + 128) = hi;
     }
+}
+
+// (row, quarter) of a 128-row operand tile: expand words 2*quarter, 2*quarter+1 of the descriptor
+__device__ __forceinline__ void t5_store_quarter(uint8_t* tile, int row, int quarter, const uint2& d)
+{
+    uint8_t* base = tile + (row >> 3) * 2048 + (row & 7) * 16 + quarter * 512;
+    uint4 lo, hi;
+    t5_expand_word(d.x, lo, hi);
+    *(uint4*)base = lo; *(uint4*)(base + 128) = hi;
+    t5_expand_word(d.y, lo, hi);
+    *(uint4*)(base + 256) = lo; *(uint4*)(base + 384) = hi;
 }
 
 __device__ __forceinline__ uint64_t t5_smem_desc(uint32_t saddr)
@@ -84,7 +96,7 @@ __device__ __forceinline__ void t5_reduce32(const uint32_t (&v)[32], const int32
     }
 }
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(T5_THREADS, 1)
 vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
                    const uint8_t* __restrict__ train, int nt_max, long t_stride,
                    const int32_t* __restrict__ d_nq, const int32_t* __restrict__ d_nt,
@@ -93,16 +105,20 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
 {
     extern __shared__ __align__(128) uint8_t t5_smem[];
     __shared__ __align__(8) unsigned long long s_bar[2];
-    __shared__ __align__(16) int32_t s_c[2][T5_N];
+    // key constants of a train tile; three deep: a fast warp expands tile i+1 while a slow one still reduces tile i-1
+    __shared__ __align__(16) int32_t s_c[3][T5_N];
     __shared__ uint32_t s_tmem;
+    __shared__ int2 s_merge[T5_ROWS];
     const int pair = blockIdx.z, split = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int nq = d_nq ? min(d_nq[pair], nq_max) : nq_max;
     const int nt = d_nt ? min(d_nt[pair], nt_max) : nt_max;
     const int q0 = blockIdx.x * T5_ROWS;
-    const int myrow = q0 + (wid >> 2) * 128 + (wid & 3) * 32 + lane;     // TMEM lane (wid & 3) * 32 + lane of M-tile wid >> 2
+    const int mtile = (wid >> 2) & 1, chalf = wid >> 3;                  // M-tile and column half this warp reads back
+    const int lrow = mtile * 128 + (wid & 3) * 32 + lane;                // TMEM lane (wid & 3) * 32 + lane of that M-tile
+    const int myrow = q0 + lrow;
     if (q0 >= nq) {
         const int q = q0 + tid;
-        if (q < nq_max && split == 0) {
+        if (tid < T5_ROWS && q < nq_max && split == 0) {
             size_t o = ((size_t)pair * nq_max + q) * 2;
             out_idx[o] = -1; out_idx[o + 1] = -1; out_dist[o] = -1; out_dist[o + 1] = -1;
         }
@@ -126,9 +142,8 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     }
     // ---- query rows -> A operand, popc(a) of this thread's row
     const uint8_t* qbase = query + (size_t)pair * q_stride * 32;
-#pragma unroll
-    for (int it = 0; it < 2; ++it) {
-        const int item = tid + 256 * it, row = item & 255, half = item >> 8;
+    {
+        const int row = tid & 255, half = tid >> 8;
         const uint4 d = __ldg((const uint4*)(qbase + (size_t)min(q0 + row, nq - 1) * 32) + half);
         t5_store_half(sA + (row >> 7) * T5_OPER_BYTES, row & 127, half, d);
     }
@@ -142,19 +157,20 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     const int tiles = (nt + T5_N - 1) / T5_N;
     const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
 
-    // thread = (train row, half) with consecutive lanes on consecutive rows: a quarter-warp's 128-bit stores
-    // cover one 128-byte core-matrix column (conflict-free); half 0 also reads the other half for popc(b)
-    auto expand_tile = [&](int tile, int buf) {
-        const int row = tid & 127, half = tid >> 7, d_idx = tile * T5_N + row;
-        uint4 d = make_uint4(0u, 0u, 0u, 0u), e = d;
-        if (d_idx < nt) {
-            d = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + half);
-            if (half == 0) e = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + 1);
-        }
-        t5_store_half(sB + buf * T5_OPER_BYTES, row, half, d);
-        if (half == 0) {
-            const int pb = __popc(d.x) + __popc(d.y) + __popc(d.z) + __popc(d.w) + __popc(e.x) + __popc(e.y) + __popc(e.z) + __popc(e.w);
-            s_c[buf][row] = d_idx < nt ? ((pb << 16) | d_idx) : (T5_INVALID | (d_idx & 0xffff));
+    // thread = (train row, quarter) with consecutive lanes on consecutive rows: a quarter-warp's 128-bit stores
+    // cover one 128-byte core-matrix column (conflict-free); quarter 0 reads the whole row for popc(b)
+    auto expand_tile = [&](int tile, int buf, int cbuf) {
+        const int row = tid & 127, quarter = tid >> 7, d_idx = tile * T5_N + row;
+        uint2 d = make_uint2(0u, 0u);
+        if (d_idx < nt) d = __ldg((const uint2*)(tp + (size_t)d_idx * 32) + quarter);
+        t5_store_quarter(sB + buf * T5_OPER_BYTES, row, quarter, d);
+        if (quarter == 0) {
+            int pb = 0;
+            if (d_idx < nt) {
+                const uint4 x = __ldg((const uint4*)(tp + (size_t)d_idx * 32)), y = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + 1);
+                pb = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
+            }
+            s_c[cbuf][row] = d_idx < nt ? ((pb << 16) | d_idx) : (T5_INVALID | (d_idx & 0xffff));
         }
     };
     auto issue_tile = [&](int buf) {                 // one thread: 2 M-tiles x 8 K-steps, then commit to the buffer's barrier
@@ -181,7 +197,7 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     int k1[4], k2[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) { k1[c] = 0x7fffffff; k2[c] = 0x7fffffff; }
-    if (t_begin < t_end) expand_tile(t_begin, 0);
+    if (t_begin < t_end) expand_tile(t_begin, 0, 0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -192,7 +208,7 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     for (int tile = t_begin; tile < t_end; ++tile) {
         const int i = tile - t_begin, buf = i & 1;
         if (tile + 1 < t_end) {
-            expand_tile(tile + 1, buf ^ 1);          // its previous reader (MMA of tile - 1) completed before the last epilogue
+            expand_tile(tile + 1, buf ^ 1, (i + 1) % 3);          // its previous reader (MMA of tile - 1) completed before the last epilogue
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
         __syncthreads();
@@ -207,34 +223,37 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
                 "D%=:\n}\n" ::"r"(bar_u + 8 * buf), "r"(parity) : "memory");
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + (wid >> 2) * 128;
-        // four 32-column chunks, the TMEM load of chunk c+1 in flight while chunk c is reduced
+        const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + mtile * 128 + chalf * 64;
+        const int32_t* cbase = &s_c[i % 3][chalf * 64];
+        // this warp's 64 columns as two 32-column chunks, the second load in flight while the first is reduced
         uint32_t va[32], vb[32];
         t5_tmem_ld32(va, taddr);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         t5_tmem_ld32(vb, taddr + 32);
-        t5_reduce32(va, &s_c[buf][0], k1, k2);
+        t5_reduce32(va, cbase, k1, k2);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        t5_tmem_ld32(va, taddr + 64);
-        t5_reduce32(vb, &s_c[buf][32], k1, k2);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        t5_tmem_ld32(vb, taddr + 96);
-        t5_reduce32(va, &s_c[buf][64], k1, k2);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        t5_reduce32(vb, &s_c[buf][96], k1, k2);
+        t5_reduce32(vb, cbase + 32, k1, k2);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
+    // merge the four chains (two sorted pairs -> the two smallest of the four keys), then the two column halves
+#pragma unroll
+    for (int c = 1; c < 4; ++c) {
+        const int n2 = __vimin3_s32(max(k1[0], k1[c]), k2[0], k2[c]);
+        k1[0] = min(k1[0], k1[c]);
+        k2[0] = n2;
+    }
+    if (chalf == 1) s_merge[lrow] = make_int2(k1[0], k2[0]);
     __syncthreads();
     if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
+    if (chalf == 1) return;
+    {
+        const int2 o = s_merge[lrow];
+        const int n2 = __vimin3_s32(max(k1[0], o.x), k2[0], o.y);
+        k1[0] = min(k1[0], o.x);
+        k2[0] = n2;
+    }
 
     if (myrow < nq_max) {
-        // merge the four chains: two sorted pairs -> the two smallest of the four keys
-#pragma unroll
-        for (int c = 1; c < 4; ++c) {
-            const int n2 = __vimin3_s32(max(k1[0], k1[c]), k2[0], k2[c]);
-            k1[0] = min(k1[0], k1[c]);
-            k2[0] = n2;
-        }
         const int kk1 = k1[0], kk2 = k2[0];
         const bool v1 = kk1 < T5_INVALID, v2 = kk2 < T5_INVALID;
         int d1 = v1 ? (kk1 >> 16) + pa : -1, i1 = v1 ? (kk1 & 0xffff) : -1;
@@ -270,7 +289,7 @@ int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t*
 {
     int rc = vs_knn2_tc5_configure();
     if (rc) return rc;
-    vs_knn2_tc5_kernel<<<dim3((nq + T5_ROWS - 1) / T5_ROWS, nsplit, pairs), 256, T5_DYN_SMEM, s>>>(
+    vs_knn2_tc5_kernel<<<dim3((nq + T5_ROWS - 1) / T5_ROWS, nsplit, pairs), T5_THREADS, T5_DYN_SMEM, s>>>(
         d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, partial, d_idx, d_dist);
     return VSLAM_OK;
 }
