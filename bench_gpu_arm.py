@@ -210,10 +210,12 @@ def run_gpu_arm(args, rank, world, B):
                            "achieved_gbs": BN.extraction_bytes(w, h, nf) * B * K / (prof[:19].sum() * 1e-3) / 1e9
                            if prof[:19].sum() > 0 else 0.0},
             "matching": {"ms_per_step": float(prof[19] + prof[20]) / K, "gpairs_per_s": pairs_per_s / 1e9,
-                         # kNN-2 runs on the int8 MMA pipe: 16 descriptor pairs per IMMA.16832; peak = 0.12 IMMA/clk/SMSP
-                         # measured by scratch/ubench/imma.cu on this pool's B200 (148 SMs x 4 SMSPs x 1.965 GHz)
-                         "imma_per_s": pairs_per_s / 16.0, "imma_peak_per_s": 0.12 * 592 * 1.965e9,
-                         "imma_frac": pairs_per_s / 16.0 / (0.12 * 592 * 1.965e9)},
+                         # kNN-2 = binary GEMM on tcgen05 kind::i8 (256 u8 MACs per descriptor pair); the tensor
+                         # reference is the nominal dense int8/fp8 rate of B200_PROFILING.md (4.5 Pop/s). The kernel
+                         # is bound by the ALU-pipe top-2 reduction of the distances, not by the MMA.
+                         "engine": os.environ.get("VSLAM_KNN", "tcgen05"),
+                         "tensor_pops": pairs_per_s * 512.0 / 1e15, "tensor_peak_pops": 4.5,
+                         "tensor_frac": pairs_per_s * 512.0 / 4.5e15},
             "kernel_ms_per_step": breakdown,
         }
         if world == 1 and not args.no_cpu:
