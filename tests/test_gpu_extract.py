@@ -73,7 +73,8 @@ def test_detect_and_compute_synthetic_640(oracle, synth640):
 
 
 @pytest.mark.parametrize("w,h,nf,nl,sf", [(320, 240, 500, 8, 1.2), (478, 850, 2000, 8, 1.2),
-                                           (333, 257, 1000, 5, 1.5), (1920, 1080, 8000, 8, 1.2)])
+                                           (333, 257, 1000, 5, 1.5), (1920, 1080, 8000, 8, 1.2),   # C3
+                                           (3840, 2160, 16000, 8, 1.2)])                           # C5
 def test_detect_and_compute_other_shapes(oracle, w, h, nf, nl, sf):
     from orbslam2.synth import SyntheticVideo
     frame = SyntheticVideo(w, h, 1).frame(2)

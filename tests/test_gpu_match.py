@@ -16,7 +16,8 @@ def _rand_desc(n, seed):
 
 @pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (5, 1), (127, 129), (128, 128), (2000, 2000),
                                    (2049, 777), (300, 5000), (8192, 8192), (257, 63), (33, 65),
-                                   (40, 70000)])   # nt >= 65536 takes the scalar POPC kernel
+                                   (16000, 16000), (70, 65535), (70, 65536),   # 16-bit train index limit
+                                   (40, 65537), (40, 70000)])   # nt > 65536 takes the scalar POPC kernel
 def test_knn2_random_exact(oracle, nq, nt):
     from orbslam2 import _native
     q, t = _rand_desc(nq, nq), _rand_desc(nt, nt + 1)

@@ -114,7 +114,7 @@ vs_knn2_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
 }
 
 // ---------------------------------------------------------------------------
-// Tensor-core variant (nt < 65536).  Brute-force Hamming matching is a binary GEMM; the POPC
+// Tensor-core variant (nt <= 65536).  Brute-force Hamming matching is a binary GEMM; the POPC
 // pipe issues 16 lanes/clk/SM, which the scalar kernel above already saturates (93 % measured),
 // while the int8 MMA pipe does the same pair 3.8x faster (scratch/ubench/imma.cu: 0.12
 // IMMA.16832 per clk per SMSP).  Bits are expanded to 0/1 bytes, so that
@@ -308,7 +308,7 @@ int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t*
                        const int32_t* d_nq, const int32_t* d_nt, int pairs, int nsplit, int4* partial,
                        int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
 
-// kNN-2 engine for nt < 65536: 1 = tcgen05 kind::i8 (bf_match_tc5.cu), 0 = mma.sync int8 (above).
+// kNN-2 engine for nt <= 65536: 1 = tcgen05 kind::i8 (bf_match_tc5.cu), 0 = mma.sync int8 (above).
 // VSLAM_KNN=imma|tc5 overrides the default.
 static int knn_use_tc5()
 {
@@ -330,7 +330,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
                    int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
 {
     if (pairs <= 0 || nq <= 0) return VSLAM_OK;
-    const bool mma = nt < 65536;   // the tensor-core kernel packs the train index into 16 bits
+    const bool mma = nt <= 65536;  // the tensor-core kernels pack the train index into 16 bits
     const int qtiles = mma ? (nq + KT_Q - 1) / KT_Q : (nq + BF_THREADS - 1) / BF_THREADS;
     const bool tc5 = mma && knn_use_tc5();
     const int ttiles = tc5 ? (nt + 127) / 128 : mma ? (nt + KT_T - 1) / KT_T : (nt + BF_TILE - 1) / BF_TILE;
