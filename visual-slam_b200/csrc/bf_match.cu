@@ -351,7 +351,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
         }
     }
     vs_prof_mark(prof, VS_PROF_KNN2, s);
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (tc5) {
         int rc = vs_knn2_tc5_launch(d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, pairs, nsplit, g_partial, d_idx, d_dist, s);
         if (rc) return rc;
@@ -362,7 +362,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
         vs_knn2_kernel<<<dim3(qtiles, nsplit, pairs), BF_THREADS, 0, s>>>(
             d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, g_partial, d_idx, d_dist);
     if (nsplit > 1) {
-        ++g_vs_launches;
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_knn2_merge_kernel<<<dim3((nq + 255) / 256, pairs), 256, 0, s>>>(g_partial, nq, d_nq, nsplit,
                                                                           d_idx, d_dist);
     }
@@ -420,7 +420,7 @@ int vs_launch_ratio(vslam_orb* prof, const int32_t* d_idx, const int32_t* d_dist
 {
     if (pairs <= 0) return VSLAM_OK;
     vs_prof_mark(prof, VS_PROF_RATIO, s);
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     vs_ratio_kernel<<<pairs, 256, 0, s>>>(d_idx, d_dist, nq, d_nq, ratio, ratio_test, d_match, d_match_count);
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
@@ -459,7 +459,7 @@ int vs_launch_match_masked(const uint8_t* d_q, int nq, const uint8_t* d_t, int n
                            int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
 {
     if (nq <= 0) return VSLAM_OK;
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     vs_match_masked_kernel<<<(nq + 7) / 8, 256, 0, s>>>(d_q, nq, d_t, nt, d_mask, d_idx, d_dist);
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;

@@ -233,7 +233,7 @@ static int score_common(int mode, const double* h_M, const void* d_p1, const voi
     GEOM_CUDA(cnt.alloc(sizeof(int)));
     GEOM_CUDA(mask.alloc(n));
     GEOM_CUDA(cudaMemcpy(m.p, h_M, 9 * sizeof(double), cudaMemcpyHostToDevice));
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (mode == 0)
         vs_score_models_kernel<0><<<1, 128>>>(m.as<double>(), nullptr, 1, d_p1, d_p2, n, thr2, cnt.as<int>(), mask.as<uint8_t>());
     else
@@ -311,7 +311,7 @@ static int ransac_driver(int mode, const void* d_p1, const void* d_p2, int n, co
     GEOM_CUDA(models.alloc((size_t)max_iters * per * 9 * sizeof(double)));
     GEOM_CUDA(nm.alloc((size_t)max_iters * sizeof(int)));
     GEOM_CUDA(counts.alloc((size_t)max_iters * per * sizeof(int)));
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (mode == 0) {
         Norm2 n1 = hartley(h_p1, n), n2 = hartley(h_p2, n);
         vs_ransac_f_hyp_kernel<<<(max_iters + 63) / 64, 64>>>((const float2*)d_p1, (const float2*)d_p2, n, n1, n2, seed,
@@ -321,7 +321,7 @@ static int ransac_driver(int mode, const void* d_p1, const void* d_p2, int n, co
                                                             max_iters, models.as<double>(), nm.as<int>());
     }
     GEOM_CUDA(cudaGetLastError());
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (mode == 0)
         vs_score_models_kernel<0><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
                                                            counts.as<int>(), nullptr);

@@ -161,7 +161,7 @@ extern "C" int vslam_triangulate_host(const double* h_P1, const double* h_P2, co
     GEOM_CUDA(x.alloc((size_t)n * 16));
     GEOM_CUDA(cudaMemcpy(a.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
     GEOM_CUDA(cudaMemcpy(b.p, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
-    ++g_vs_launches;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     vs_triangulate_kernel<<<(n + 127) / 128, 128>>>(P1, P2, a.as<float2>(), b.as<float2>(), n, x.as<float>());
     GEOM_CUDA(cudaGetLastError());
     GEOM_CUDA(cudaMemcpy(h_X, x.p, (size_t)n * 16, cudaMemcpyDeviceToHost));
@@ -191,7 +191,7 @@ extern "C" int vslam_recover_pose_host(const double* h_E, const float* h_p1, con
         GEOM_CUDA(d.alloc(n));
         GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
         GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
-        ++g_vs_launches;
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_pose_kernel<<<(n + 63) / 64, 64>>>(c[0], c[1], c[2], c[3], a.as<double2>(), b.as<double2>(), n, 50.0,
                                               d.as<uint8_t>());
         GEOM_CUDA(cudaGetLastError());

@@ -28,7 +28,7 @@ extern "C" int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, 
     cudaError_t e = cudaMalloc(&d_out, n);
     if (e == cudaSuccess) e = cudaMemcpy(d_in, h_bgr, 3 * n, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
-        ++g_vs_launches;
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_bgr2gray_kernel<<<(unsigned)((n + 255) / 256), 256>>>(d_in, d_out, n);
         e = cudaGetLastError();
     }
@@ -111,7 +111,7 @@ extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, cons
     cudaError_t e = cudaMalloc(&d_d, (size_t)m * 32);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_k, kept.data(), (size_t)m * sizeof(VsGivenKp), cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess) {
-        ++g_vs_launches;
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_describe_given_kernel<<<(m + 7) / 8, 256, 0, s>>>(p, o->d_frames, p.width, o->d_pyr, d_k, m, d_d);
         e = cudaGetLastError();
     }

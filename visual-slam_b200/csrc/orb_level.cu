@@ -135,6 +135,18 @@ __device__ __noinline__ uint32_t load4_reflect(const uint8_t* row, int gx, int W
     return u;
 }
 
+// same for rows of at least 8 pixels, where one reflection per side covers the 4-pixel halo (branch-free)
+__device__ __forceinline__ uint32_t load4_edge(const uint8_t* row, int gx, int W)
+{
+    uint32_t u = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int x = (W - 1) - abs((W - 1) - abs(gx + j));
+        u |= (uint32_t)__ldg(row + x) << (8 * j);
+    }
+    return u;
+}
+
 // Row pass of the 7-tap Gaussian for 8 adjacent pixels: q = 8 words of the 16-bit tile starting 4
 // columns left of the first pixel, dst = 8 floats.  cv2 order: k0*x0, then one tap at a time.
 template <bool FMA>
@@ -252,13 +264,16 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             } else {
                 const int gx = x0 - VS_HALO + 4 * wd;
                 const bool fast = aligned && gx >= 0 && gx + 3 < W;
+                const bool small = W < 8 || H < 8;                      // several reflections per side possible
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     const int r = rg + 14 * k;
                     u[k] = 0;
                     if (r < RAW_H) {
-                        const uint8_t* row = src + (size_t)vs_reflect101(y0 - VS_HALO + r, H) * fpitch;
-                        u[k] = fast ? __ldg((const uint32_t*)(row + gx)) : load4_reflect(row, gx, W);
+                        const int gy = y0 - VS_HALO + r;
+                        const int ry = small ? vs_reflect101(gy, H) : (H - 1) - abs((H - 1) - abs(gy));
+                        const uint8_t* row = src + (size_t)ry * fpitch;
+                        u[k] = fast ? __ldg((const uint32_t*)(row + gx)) : small ? load4_reflect(row, gx, W) : load4_edge(row, gx, W);
                     }
                 }
             }
@@ -629,7 +644,7 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
                                            (size_t)p.lv[l - 1].pitch, p.pyr_frame_bytes, batch, p);
         dim3 grid(L.tiles_x, L.tiles_y, batch);
         vs_prof_mark(o, l, s);
-        ++g_vs_launches;
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         if (l == 0)
             vs_level_kernel<true><<<grid, 256, 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
                                                        o->d_cand, o->d_counters, tm, 0);
