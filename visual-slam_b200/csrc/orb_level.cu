@@ -15,6 +15,11 @@
 //   4. applies the 7x7 sigma=2 float Gaussian in cv2's exact operation order (K7a) and
 //      stores the blurred level used by rBRIEF.
 // Level l therefore costs one read of level l-1 and two writes of level l in HBM.
+// Phase order between barriers: tile | compass pre-test + Gaussian row pass | queued FAST networks |
+// NMS into the tile list | list-slot atomic + Gaussian column pass | list write-out -- the row pass shares
+// the pre-test's interval (both only read the tile) and the round trip of the one global atomic per tile
+// hides behind the column pass (measured: work stealing from a shared chunk counter was slower than
+// static striding, and 6 CTAs/SM at 40 registers bought 2 % on level 0 only).
 #include <cuda.h>
 
 #include "common.cuh"
@@ -25,10 +30,10 @@
 #define SC_H (VS_TH + 2)              // score rows  y0-1 .. y0+TH
 #define SC_S 72                       // score row stride; column index = tx + 4
 #define BL_ROWS (VS_TH + 6)
+#define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
 #ifndef VS_LEVEL_CTAS
 #define VS_LEVEL_CTAS 5                // resident CTAs per SM the register budget is capped for (48 registers)
 #endif
-#define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
 
 // getGaussianKernel(7, 2, CV_32F) of cv2 4.13, taps outer..centre (bit patterns)
 __device__ __constant__ uint32_t c_gauss_bits[4] = {0x3d8fafb1u, 0x3e06387eu, 0x3e434a39u, 0x3e5d4ae0u};
@@ -232,9 +237,9 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __shared__ __align__(16) float s_row[BL_ROWS * VS_TW];
     __shared__ uint32_t s_hist[256];
     __shared__ VsCand s_list[LIST_CAP];
+    __shared__ int s_n, s_base;
     __shared__ uint32_t s_tx[RAW_W], s_ty[RAW_H];
     __shared__ __align__(8) unsigned long long s_mbar;   // TMA completion barrier (levels >= 1)
-    __shared__ int s_n, s_base;
     extern __shared__ __align__(16) uint8_t s_dyn[];   // parent region + horizontal pass (levels >= 1)
 
     const VsLevel& L = plan.lv[level];
@@ -245,7 +250,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     uint8_t* fpyr = pyr + (size_t)b * plan.pyr_frame_bytes;
 
     s_hist[tid] = 0;
-    if (tid == 0) { s_n = 0; s_nq = 0; }
+    if (tid == 0) { s_nq = 0; s_n = 0; }
 
     // ---- 1. raw tile (16-bit lanes) ------------------------------------------
     if (L0) {
@@ -413,12 +418,12 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     const int thr = plan.fast_thr;
     const uint32_t kbias = (uint32_t)(512 - thr) * 0x00010001u;
     const int cx_lo = VS_EDGE - 1, cx_hi = W - VS_EDGE, cy_lo = VS_EDGE - 1, cy_hi = H - VS_EDGE;
+    const int lane = tid & 31;
     // 3a. compass pre-test.  Any arc of 9 contains at least two of the four compass points, so a corner
     // needs its second-largest compass value above c + thr or its second-smallest below c - thr.  Pixel
     // pairs that pass are queued; the full min/max networks (3b) then run on whole warps of queued pairs
     // only (a third to a half of the pairs on textured images) instead of on every pixel.
     {
-        const int lane = tid & 31;
         const int w = tid & 15;
         uint32_t need[4];                 // pass k = score row (tid >> 4) + 16k; [2k] = pair A, [2k+1] = pair B
 #pragma unroll
@@ -453,8 +458,9 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             if (need[3]) s_queue[basepos + c0 + c1 + c2 + __popc(mk[3] & lt)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 3));
         }
     }
-    if (tid < 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
-        const int r = tid % SC_H, side = tid / SC_H;
+    if (tid >= 256 - 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
+        const int t2 = tid - (256 - 2 * SC_H);
+        const int r = t2 % SC_H, side = t2 / SC_H;
         const int wi = side ? VS_TW / 2 + 2 : 1;
         const int gx = x0 + (side ? VS_TW : -1), gy = y0 - 1 + r;
         if (gy >= cy_lo && gy <= cy_hi && gx >= cx_lo && gx <= cx_hi) {
@@ -465,36 +471,52 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         }
         ((uint32_t*)(s_sc + r * SC_S))[wi] = 0u;
     }
-    __syncthreads();
-    // 3b. exact scores of the queued pairs: word wi of score row r <-> tile columns 2wi, 2wi+1
-    const int nqueue = s_nq;
-    for (int qi = tid; qi < nqueue; qi += 256) {
-        const int e = s_queue[qi], r = e >> 6, wi = e & 63;
-        const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
-        const int RW = RAW_S / 2;
-        uint32_t v[16];
-        {
-            const uint32_t m1 = rw[3 * RW - 1], z = rw[3 * RW], p1 = rw[3 * RW + 1];
-            v[0] = z; v[1] = fsr16(z, p1); v[15] = fsr16(m1, z);
-        }
-        {
-            const uint32_t m1 = rw[-3 * RW - 1], z = rw[-3 * RW], p1 = rw[-3 * RW + 1];
-            v[8] = z; v[7] = fsr16(z, p1); v[9] = fsr16(m1, z);
-        }
-        v[2] = rw[2 * RW + 1]; v[14] = rw[2 * RW - 1];
-        v[6] = rw[-2 * RW + 1]; v[10] = rw[-2 * RW - 1];
-        v[3] = fsr16(rw[RW + 1], rw[RW + 2]); v[13] = fsr16(rw[RW - 2], rw[RW - 1]);
-        v[5] = fsr16(rw[-RW + 1], rw[-RW + 2]); v[11] = fsr16(rw[-RW - 2], rw[-RW - 1]);
-        v[4] = fsr16(rw[1], rw[2]); v[12] = fsr16(rw[-2], rw[-1]);
-        uint32_t o = fast_pair(v, rw[0], kbias);
-        const int gx = x0 - VS_HALO + 2 * wi;
-        if (gx < cx_lo || gx > cx_hi) o &= 0xffff0000u;
-        if (gx + 1 < cx_lo || gx + 1 > cx_hi) o &= 0x0000ffffu;
-        ((uint32_t*)(s_sc + r * SC_S))[wi] = o;
+
+    // ---- 4a. Gaussian 7x7, row pass (reads the raw tile only, so it shares the barrier interval of 3a).
+    // cv2's vector blocks use FMA, its scalar tails do not: rows switch at W - W%32,
+    // columns at W - W%8; an aligned 8-pixel group never straddles either boundary.
+    const int wrow = W & ~31, wcol = W & ~7;
+    for (int i = tid; i < BL_ROWS * (VS_TW / 8); i += 256) {
+        const int g = i & 7, rr = i >> 3;                             // s_row row rr <-> gy = y0 - 3 + rr
+        if (y0 - 3 + rr >= H + 3) continue;                           // below every output row of the level
+        const uint2* q = (const uint2*)(s_raw + (rr + 1) * RAW_S + 8 * g);
+        float* dst = s_row + rr * VS_TW + 8 * g;
+        if (x0 + 8 * g < wrow) blur_row_item<true>(q, dst);
+        else blur_row_item<false>(q, dst);
     }
     __syncthreads();
 
-    // non-max suppression (strict >, non-corners count as 0) + 31-px border
+    // ---- 3b. exact scores of the queued pairs: word wi of score row r <-> tile columns 2wi, 2wi+1
+    {
+        const int nqueue = s_nq;
+        for (int qi = tid; qi < nqueue; qi += 256) {
+            const int e = s_queue[qi], r = e >> 6, wi = e & 63;
+            const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
+            const int RW = RAW_S / 2;
+            uint32_t v[16];
+            {
+                const uint32_t m1 = rw[3 * RW - 1], z = rw[3 * RW], p1 = rw[3 * RW + 1];
+                v[0] = z; v[1] = fsr16(z, p1); v[15] = fsr16(m1, z);
+            }
+            {
+                const uint32_t m1 = rw[-3 * RW - 1], z = rw[-3 * RW], p1 = rw[-3 * RW + 1];
+                v[8] = z; v[7] = fsr16(z, p1); v[9] = fsr16(m1, z);
+            }
+            v[2] = rw[2 * RW + 1]; v[14] = rw[2 * RW - 1];
+            v[6] = rw[-2 * RW + 1]; v[10] = rw[-2 * RW - 1];
+            v[3] = fsr16(rw[RW + 1], rw[RW + 2]); v[13] = fsr16(rw[RW - 2], rw[RW - 1]);
+            v[5] = fsr16(rw[-RW + 1], rw[-RW + 2]); v[11] = fsr16(rw[-RW - 2], rw[-RW - 1]);
+            v[4] = fsr16(rw[1], rw[2]); v[12] = fsr16(rw[-2], rw[-1]);
+            uint32_t o = fast_pair(v, rw[0], kbias);
+            const int gx = x0 - VS_HALO + 2 * wi;
+            if (gx < cx_lo || gx > cx_hi) o &= 0xffff0000u;
+            if (gx + 1 < cx_lo || gx + 1 > cx_hi) o &= 0x0000ffffu;
+            ((uint32_t*)(s_sc + r * SC_S))[wi] = o;
+        }
+    }
+    __syncthreads();
+
+    // ---- 5. non-max suppression (strict >, non-corners count as 0) + 31-px border -> tile list + histogram
     for (int i = tid; i < VS_TH * (VS_TW / 4); i += 256) {
         const int w = i & 15, ty = i >> 4;
         // words of the score row around the 4 pixels: W1 = (tx-2, tx-1), W2 = (p0, p1), W3 = (p2, p3), W4 = (tx+4, tx+5)
@@ -521,44 +543,25 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             const uint32_t kk = j < 2 ? kA : kB, cc = j < 2 ? cm.x : cm.y;
             const int gx = x0 + 4 * w + j;
             if (!(kk & ((j & 1) ? 0x80000000u : 0x8000u)) || gx < VS_EDGE || gx >= W - VS_EDGE) continue;
-            const int v = (int)((j & 1) ? (cc >> 16) : (cc & 0xffff));
-            {
-                const int score = v + thr - 1;
-                int slot = atomicAdd(&s_n, 1);
-                VsCand c;
-                c.x = (uint16_t)gx; c.y = (uint16_t)gy; c.v = (uint32_t)score;
-                s_list[slot] = c;
-                atomicAdd(&s_hist[score], 1u);
-            }
+            const int score = (int)((j & 1) ? (cc >> 16) : (cc & 0xffff)) + thr - 1;
+            const int slot = atomicAdd(&s_n, 1);
+            VsCand c;
+            c.x = (uint16_t)gx; c.y = (uint16_t)gy; c.v = (uint32_t)score;
+            s_list[slot] = c;
+            atomicAdd(&s_hist[score], 1u);
         }
     }
     __syncthreads();
+    // reserve the tile's slots in the (frame, level) list; the round trip of that atomic hides behind 4b
     int32_t* ctr = counters + ((size_t)b * plan.n_levels + level) * VS_CTR_STRIDE;
     const int n = s_n;
     if (n > 0) {
         if (tid == 0) s_base = atomicAdd(&ctr[VS_CTR_NCAND], n);
-        uint32_t hv = s_hist[tid];
+        const uint32_t hv = s_hist[tid];
         if (hv) atomicAdd(&ctr[VS_CTR_HIST + tid], (int)hv);
     }
-    __syncthreads();
-    if (n > 0) {
-        VsCand* out = cand + (size_t)b * plan.cand_frame_entries + L.cand_off + s_base;
-        for (int i = tid; i < n; i += 256) out[i] = s_list[i];
-    }
 
-    // ---- 4. Gaussian 7x7 (row pass, then column pass) -----------------------
-    // cv2's vector blocks use FMA, its scalar tails do not: rows switch at W - W%32,
-    // columns at W - W%8; an aligned 8-pixel group never straddles either boundary.
-    const int wrow = W & ~31, wcol = W & ~7;
-    for (int i = tid; i < BL_ROWS * (VS_TW / 8); i += 256) {
-        const int g = i & 7, rr = i >> 3;                             // s_row row rr <-> gy = y0 - 3 + rr
-        if (y0 - 3 + rr >= H + 3) continue;                           // below every output row of the level
-        const uint2* q = (const uint2*)(s_raw + (rr + 1) * RAW_S + 8 * g);
-        float* dst = s_row + rr * VS_TW + 8 * g;
-        if (x0 + 8 * g < wrow) blur_row_item<true>(q, dst);
-        else blur_row_item<false>(q, dst);
-    }
-    __syncthreads();
+    // ---- 4b. Gaussian 7x7, column pass
     uint8_t* blur = fpyr + L.blur_off;
     for (int i = tid; i < (VS_TH / 2) * (VS_TW / 4); i += 256) {
         const int w = i & 15, ty = (i >> 4) * 2;                      // two output rows per item
@@ -570,6 +573,11 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         uint8_t* dst = blur + (size_t)gy * L.pitch + gx;
         *(uint32_t*)dst = o0;
         if (gy + 1 < H) *(uint32_t*)(dst + L.pitch) = o1;
+    }
+    if (n > 0) {
+        __syncthreads();
+        VsCand* out = cand + (size_t)b * plan.cand_frame_entries + L.cand_off + s_base;
+        for (int i = tid; i < n; i += 256) out[i] = s_list[i];
     }
 }
 

@@ -332,10 +332,16 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
     const int u = lane - VS_HALF_PATCH;              // lanes 0..30 <-> columns -15..15 of the disc
     const int vmax = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;   // the disc is symmetric: |v| <= umax[|u|]
 
+    // Pass A: intensity-centroid angle of this warp's keypoints, one after the other (lane k keeps keypoint
+    // k's angle, centre and level).  Then sin/cos in double for all of them at once -- lane k evaluates
+    // keypoint k, so the warp pays for one evaluation instead of one per keypoint.  Pass B: steered rBRIEF.
+    const int i0 = (blockIdx.x * 8 + wid) * VS_DESC_PER_WARP;
+    const int nk = min(VS_DESC_PER_WARP, min(total, plan.kp_cap) - i0);   // warp-uniform; <= 0: nothing to do
     int level = 0;
-    for (int k = 0; k < VS_DESC_PER_WARP; ++k) {
-        const int i = (blockIdx.x * 8 + wid) * VS_DESC_PER_WARP + k;
-        if (i >= total || i >= plan.kp_cap) break;
+    float m_ang = 0.f;
+    int m_cx = 0, m_cy = 0, m_level = 0;
+    for (int k = 0; k < nk; ++k) {
+        const int i = i0 + k;
         while (level + 1 < plan.n_levels && i >= s_start[level + 1]) ++level;   // warp-uniform, monotone in k
         const int j = i - s_start[level];
         const bool raw_aligned = level > 0 || frames_aligned;
@@ -379,14 +385,29 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
             ko->x = kx; ko->y = ky; ko->size = __fmul_rn(31.f, L.scale);
             ko->angle = ang; ko->response = __uint_as_float(c.v); ko->octave = level;
         }
-        // ---- steered rBRIEF (K7b): centre cvRound(pt * (1/scale)), rotation from the angle in radians
+        // centre of the rBRIEF pattern: cvRound(pt * (1/scale))
         const float inv = __fdiv_rn(1.f, L.scale);
-        const int cx = __float2int_rn(__fmul_rn(kx, inv)), cy = __float2int_rn(__fmul_rn(ky, inv));
-        const float rad = __fmul_rn(ang, (float)(3.14159265358979323846 / 180.f));
+        if (lane == k) {
+            m_ang = ang; m_level = level;
+            m_cx = __float2int_rn(__fmul_rn(kx, inv)); m_cy = __float2int_rn(__fmul_rn(ky, inv));
+        }
+    }
+    if (nk <= 0) return;
+    // rotation from the angle in radians (K7b): (float)cos / (float)sin of the float32 angle, evaluated in double
+    float m_ca, m_sa;
+    {
+        const float rad = __fmul_rn(m_ang, (float)(3.14159265358979323846 / 180.f));
         double sd, cd;
         sincos((double)rad, &sd, &cd);
-        const float ca = (float)cd, sa = (float)sd;
+        m_ca = (float)cd; m_sa = (float)sd;
+    }
+    for (int k = 0; k < nk; ++k) {
+        const int i = i0 + k;
+        const float ca = __shfl_sync(0xffffffffu, m_ca, k), sa = __shfl_sync(0xffffffffu, m_sa, k);
+        const int cx = __shfl_sync(0xffffffffu, m_cx, k), cy = __shfl_sync(0xffffffffu, m_cy, k);
+        const VsLevel& L = plan.lv[__shfl_sync(0xffffffffu, m_level, k)];
         const int xs = (cx - DESC_R) & ~3;
+        __syncwarp();
         stage_window<DESC_WIN, DESC_WIN_S / 4, true>(wb, fp + L.blur_off, L.pitch, xs, cy - DESC_R, lane);
         __syncwarp();
         // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
@@ -398,9 +419,9 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
             const float4 p = __ldg(&g_patf_t[t * 32 + lane]);
             const float fx0 = __fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), fy0 = __fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca));
             const float fx1 = __fsub_rn(__fmul_rn(p.z, ca), __fmul_rn(p.w, sa)), fy1 = __fadd_rn(__fmul_rn(p.z, sa), __fmul_rn(p.w, ca));
-            const uint32_t i0 = __float_as_uint(__fadd_rn(fy0, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
-            const uint32_t i1 = __float_as_uint(__fadd_rn(fy1, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
-            byte |= (uint32_t)(wb[i0] < wb[i1]) << t;
+            const uint32_t i0w = __float_as_uint(__fadd_rn(fy0, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
+            const uint32_t i1w = __float_as_uint(__fadd_rn(fy1, magic)) * DESC_WIN_S + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
+            byte |= (uint32_t)(wb[i0w] < wb[i1w]) << t;
         }
         desc_out[((size_t)b * plan.kp_cap + i) * 32 + lane] = (uint8_t)byte;
     }
