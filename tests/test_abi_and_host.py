@@ -109,3 +109,35 @@ def test_initializer_guards():
     init.set_first_frame([1], np.zeros((1, 32), np.uint8), np.zeros((4, 4), np.uint8))
     ok, R, t, pts, ms = init.initialize([1], np.zeros((1, 32), np.uint8), FewMatches(), None)
     assert ok is False and ms == [1, 2, 3]
+
+
+def test_frontend_gates_equal_the_reference_loops():
+    """frontend.gate_* (array form of matcher.py:109-169) against the reference's Python loops, including
+    displacements that sit exactly on the threshold and heavy distance ties."""
+    import math
+    from orbslam2 import frontend
+    rng = np.random.default_rng(3)
+    n = 400
+    pts1 = rng.uniform(0, 640, (n, 2)).astype(np.float32)
+    pts2 = (pts1 + rng.normal(0, 8, (n, 2))).astype(np.float32)
+    pts2[:40] = pts1[:40] + np.float32([11.2, 0.0])           # |d| == max_dist for (480, 640) at 2 %  (11.2)
+    pts2[40:60] = pts1[40:60] + np.float32([6.72, 8.96])      # 3-4-5 triangle scaled to 11.2
+    q = rng.permutation(n)[:300].astype(np.int32)
+    q.sort()
+    t = rng.integers(0, n, 300).astype(np.int32)
+    t[:60] = q[:60]
+    dist = rng.integers(5, 60, 300).astype(np.float32)
+    max_dist = ((640 + 480) / 2.0) * 0.02
+    ref_keep = [math.hypot(float(pts2[b][0]) - float(pts1[a][0]), float(pts2[b][1]) - float(pts1[a][1])) <= max_dist
+                for a, b in zip(q, t)]
+    keep = frontend.gate_geometric_distance(pts1, pts2, q, t, 0.02, (480, 640))
+    assert keep.tolist() == ref_keep and 0 < sum(ref_keep) < 300
+    for d in (dist, dist[:1], dist[:2], np.full(7, 9, np.float32)):
+        order, n_keep = frontend.gate_descriptor_distance(d)
+        ref_sorted = sorted(range(len(d)), key=lambda i: d[i])
+        thr = np.median([float(x) for x in d]) * 2.0
+        ref = [i for i in ref_sorted if d[i] < thr]
+        assert order[:n_keep].tolist() == ref
+    order, n_keep = frontend.gate_descriptor_distance(dist, 20.0)
+    assert order[:n_keep].tolist() == [i for i in sorted(range(300), key=lambda i: dist[i]) if dist[i] < 20.0]
+    assert frontend.gate_descriptor_distance(np.zeros(0, np.float32)) [1] == 0

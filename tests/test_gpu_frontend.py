@@ -1,0 +1,153 @@
+"""GPU parity of the array-level front end against the reference's own sequence.
+
+N1: `frontend.track_pair` must make the same decisions as tracker.py:214-254 run with cv2 objects: the gated
+match list (integer / comparison work) is compared exactly; the essential-matrix stage has its own seeded
+sampler, so its inlier set is held to the bars of tests/test_gpu_geometry.py (Jaccard >= 0.80 against
+cv2.findEssentialMat at threshold 1, >= 97 % of its inlier count).
+N2: the BFMatcher stand-in returns exactly cv2.BFMatcher.knnMatch's tuples; the adaptor reroutes a module's
+cv2.BFMatcher / cv2.findFundamentalMat.
+"""
+import math
+import types
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+K_SYNTH = np.array([[320.0, 0, 320], [0, 320, 240], [0, 0, 1]])
+
+
+def _reference_gates(cv2, kps1, kps2, d1, d2, shape, ratio=0.75, pct=0.02):
+    """tracker.py:214-230 / matcher.py:70-81,109-169 with cv2 objects (the reference's data flow)."""
+    knn = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False).knnMatch(d1, d2, k=2)
+    matches = []
+    for pair in knn:
+        if len(pair) == 2:
+            m, n = pair
+            if m.distance < ratio * n.distance:
+                matches.append(m)
+        elif len(pair) == 1:
+            matches.append(pair[0])
+    h, w = shape[:2]
+    max_dist = ((w + h) / 2.0) * pct
+    kept = []
+    for m in matches:
+        a, b = kps1[m.queryIdx].pt, kps2[m.trainIdx].pt
+        if math.hypot(b[0] - a[0], b[1] - a[1]) <= max_dist:
+            kept.append(m)
+    if not kept:
+        return []
+    kept = sorted(kept, key=lambda x: x.distance)
+    thr = np.median([m.distance for m in kept]) * 2.0
+    return [m for m in kept if m.distance < thr]
+
+
+@pytest.mark.parametrize("f0,f1", [(0, 1), (3, 5)])
+def test_track_pair_equals_reference_sequence(synth640, f0, f1):
+    import cv2
+    from orbslam2 import frontend
+    from orbslam2.extractor import ORBExtractor
+    ex = ORBExtractor(n_features=2000)
+    img1, img2 = synth640.frame(f0), synth640.frame(f1)
+    kps1, d1 = ex.detect_and_compute(img1)
+    kps2, d2 = ex.detect_and_compute(img2)
+    pts1 = np.float32([k.pt for k in kps1])
+    pts2 = np.float32([k.pt for k in kps2])
+    ref = _reference_gates(cv2, kps1, kps2, d1, d2, img1.shape)
+    out = frontend.track_pair(pts1, d1, pts2, d2, K_SYNTH, img1.shape)
+    assert len(ref) >= 8
+    assert out["query_idx"].tolist() == [m.queryIdx for m in ref]
+    assert out["train_idx"].tolist() == [m.trainIdx for m in ref]
+    assert out["distance"].tolist() == [m.distance for m in ref]
+    # essential matrix + pose against cv2 on the same point lists
+    p1 = np.float32([kps1[m.queryIdx].pt for m in ref])
+    p2 = np.float32([kps2[m.trainIdx].pt for m in ref])
+    E, mask = cv2.findEssentialMat(p1, p2, K_SYNTH, cv2.RANSAC, 0.999, 1.0)
+    _, R, t, pmask = cv2.recoverPose(E, p1, p2, K_SYNTH, mask=mask.copy())
+    assert out["success"] and out["T"].shape == (4, 4)
+    a, b = out["ransac_mask"] != 0, mask.ravel() != 0
+    jac = (a & b).sum() / max((a | b).sum(), 1)
+    assert jac >= 0.80 and a.sum() >= 0.97 * b.sum(), (jac, int(a.sum()), int(b.sum()))
+    assert not (out["inlier_mask"].astype(bool) & ~a).any() and pmask.shape == mask.shape
+    # the synthetic clip is a pan over a plane, where E is not unique (cv2's own cheirality mask keeps a few
+    # dozen of ~700 points there): the pose is checked for validity (proper rotation, unit translation, T
+    # assembled like tracker.py:250-253), not against cv2's choice among the equivalent solutions
+    Ro, to = out["R"], out["t"].ravel()
+    assert np.allclose(Ro @ Ro.T, np.eye(3), atol=1e-9) and abs(np.linalg.det(Ro) - 1.0) < 1e-9
+    assert abs(np.linalg.norm(to) - 1.0) < 1e-9
+    assert np.array_equal(out["T"][:3, :3], Ro) and np.array_equal(out["T"][:3, 3], to) and out["T"][3].tolist() == [0, 0, 0, 1]
+    assert R.shape == (3, 3) and t.shape == (3, 1)
+
+
+def test_track_pair_guards():
+    from orbslam2 import frontend
+    rng = np.random.default_rng(0)
+    d = rng.integers(0, 256, (50, 32), dtype=np.uint8)
+    pts = rng.uniform(0, 600, (50, 2)).astype(np.float32)
+    out = frontend.track_pair(pts, d, pts[:0], d[:0], K_SYNTH, (480, 640))
+    assert not out["success"] and len(out["query_idx"]) == 0
+    # identical frames: every match has zero displacement and distance 0 -> median 0 -> `<` keeps none
+    out = frontend.track_pair(pts, d, pts, d, K_SYNTH, (480, 640))
+    assert not out["success"] and len(out["query_idx"]) == 0
+    q, t, dist = frontend.match_arrays(d, d)
+    assert q.tolist() == list(range(50)) and t.tolist() == list(range(50)) and not dist.any()
+
+
+@pytest.mark.parametrize("nq,nt", [(300, 280), (40, 1), (17, 2), (5, 0)])
+def test_bfmatcher_stand_in_equals_cv2(nq, nt):
+    import cv2
+    from orbslam2.frontend import BFMatcher
+    rng = np.random.default_rng(nq * 1000 + nt)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    if nt > 3:
+        t[3] = t[1]                                           # ties -> lowest train index first
+        q[0] = t[1]
+    ours = BFMatcher(cv2.NORM_HAMMING, crossCheck=False)
+    if nt == 0:
+        assert all(len(r) == 0 for r in ours.knnMatch(q, t, k=2))
+        return
+    ref = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)
+    for k in (1, 2):
+        a, b = ours.knnMatch(q, t, k=k), ref.knnMatch(q, t, k=k)
+        assert len(a) == len(b)
+        for ra, rb in zip(a, b):
+            assert [(m.queryIdx, m.trainIdx, m.imgIdx, m.distance) for m in ra] == \
+                   [(m.queryIdx, m.trainIdx, m.imgIdx, m.distance) for m in rb]
+    assert [(m.queryIdx, m.trainIdx, m.distance) for m in ours.match(q, t)] == \
+           [(m.queryIdx, m.trainIdx, m.distance) for m in ref.match(q, t)]
+
+
+def test_local_mapper_adaptor_reroutes_module_cv2(synth640):
+    """A module written like local_mapper.py:116-137 (its own BFMatcher + 0.8 ratio + FM_RANSAC) runs on
+    the B200 kernels after install_local_mapper_adaptor, with cv2-compatible results."""
+    import cv2
+    from orbslam2 import frontend
+    from orbslam2.extractor import ORBExtractor
+    mod = types.ModuleType("fake_local_mapper")
+    mod.cv2 = cv2
+
+    def create_points(kf1, kf2):                              # the reference's statements, on module-level cv2
+        matcher = mod.cv2.BFMatcher(mod.cv2.NORM_HAMMING, crossCheck=False)
+        matches = matcher.knnMatch(kf1["descriptors"], kf2["descriptors"], k=2)
+        good = [p[0] for p in matches if len(p) >= 2 and p[0].distance < 0.8 * p[1].distance]
+        p1 = np.float32([kf1["keypoints"][m.queryIdx].pt for m in good])
+        p2 = np.float32([kf2["keypoints"][m.trainIdx].pt for m in good])
+        F, mask = mod.cv2.findFundamentalMat(p1, p2, mod.cv2.FM_RANSAC, 3.0)
+        return good, F, mask
+
+    ex = ORBExtractor(n_features=1500)
+    kfs = []
+    for f in (0, 2):
+        kps, desc = ex.detect_and_compute(synth640.frame(f))
+        kfs.append({"keypoints": kps, "descriptors": desc})
+    good_ref, F_ref, mask_ref = create_points(*kfs)
+    proxy = frontend.install_local_mapper_adaptor(mod)
+    assert isinstance(mod.cv2.BFMatcher(cv2.NORM_HAMMING), frontend.BFMatcher) and mod.cv2.FM_RANSAC == cv2.FM_RANSAC
+    good, F, mask = create_points(*kfs)
+    mod.cv2 = proxy._cv2
+    assert [(m.queryIdx, m.trainIdx, m.distance) for m in good] == [(m.queryIdx, m.trainIdx, m.distance) for m in good_ref]
+    assert F.shape == (3, 3) and mask.shape == mask_ref.shape and mask.dtype == np.uint8
+    a, b = mask.ravel() != 0, mask_ref.ravel() != 0
+    assert (a & b).sum() / max((a | b).sum(), 1) >= 0.93 and a.sum() >= 0.97 * b.sum()

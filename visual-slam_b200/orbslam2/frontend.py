@@ -1,0 +1,180 @@
+"""Array-level front end for the callers either side of the hot path.
+
+The reference's per-frame tracking step (`Tracker._track_frame`, tracker.py:214-254) is
+
+    match -> filter_matches_by_geometric_distance -> filter_matches_by_distance
+          -> cv2.findEssentialMat(RANSAC, 0.999, 1.0) -> cv2.recoverPose
+
+written with Python lists of cv2.DMatch / cv2.KeyPoint (about 4 ms of object construction per frame).
+`track_pair` is the same sequence on plain arrays: the kNN-2 search, the RANSAC and the pose recovery run in
+libvslam_b200.so, the two gates are the reference's arithmetic vectorised (exactly the same decisions: the
+comparisons are made on the same float64 values).  No cv2 object is created on the way.
+
+`BFMatcher` / `install_local_mapper_adaptor` route LocalMapper's private matcher (local_mapper.py:116-149:
+its own `cv2.BFMatcher.knnMatch`, a 0.8 ratio test and `cv2.findFundamentalMat(FM_RANSAC, 3.0)`) through the
+same kernels without editing local_mapper.py.
+"""
+import math
+
+import numpy as np
+
+from . import _native
+
+
+# --------------------------------------------------------------------------- N1: tracking step
+def match_arrays(descriptors1, descriptors2, ratio_threshold=0.75, ratio_test=True):
+    """matcher.py:44-83 on arrays -> (query_idx int32[n], train_idx int32[n], distance float32[n]),
+    ascending query index (the order of the reference's match list)."""
+    e = np.zeros(0, np.int32)
+    if descriptors1 is None or descriptors2 is None or len(descriptors1) == 0 or len(descriptors2) == 0:
+        return e, e.copy(), np.zeros(0, np.float32)
+    idx, dist = _native.bf_knn2_host(np.asarray(descriptors1).astype(np.uint8, copy=False),
+                                     np.asarray(descriptors2).astype(np.uint8, copy=False))
+    d1 = dist[:, 0].astype(np.float32).astype(np.float64)
+    d2 = dist[:, 1].astype(np.float32).astype(np.float64)
+    two = idx[:, 1] >= 0
+    one = (idx[:, 0] >= 0) & ~two
+    keep = ((two & (d1 < ratio_threshold * d2)) | one) if ratio_test else (two | one)
+    q = np.nonzero(keep)[0].astype(np.int32)
+    return q, idx[q, 0].astype(np.int32), dist[q, 0].astype(np.float32)
+
+
+def gate_geometric_distance(pts1, pts2, q, t, threshold_percent, image_shape):
+    """matcher.py:109-142: keep matches whose displacement is <= ((W + H) / 2) * pct.  pts are float32 [n, 2]
+    (cv2.KeyPoint.pt values); the differences and the hypot are taken in float64 like the reference's
+    Python floats.  Returns the boolean keep mask over the matches."""
+    height, width = image_shape[:2]
+    max_dist = ((width + height) / 2.0) * threshold_percent
+    p1 = np.asarray(pts1, np.float32)[q].astype(np.float64)
+    p2 = np.asarray(pts2, np.float32)[t].astype(np.float64)
+    dx, dy = p2[:, 0] - p1[:, 0], p2[:, 1] - p1[:, 1]
+    d = np.hypot(dx, dy)
+    keep = d <= max_dist
+    # math.hypot (the reference) and C hypot may differ in the last ulp: re-decide the borderline ones exactly
+    for k in np.nonzero(np.abs(d - max_dist) <= 1e-9 * max(max_dist, 1.0))[0]:
+        keep[k] = math.hypot(dx[k], dy[k]) <= max_dist
+    return keep
+
+
+def gate_descriptor_distance(dist, distance_threshold=None):
+    """matcher.py:144-169: stable sort by distance, threshold = 2 x median when not given, keep `<`.
+    Returns (order, n_keep): indices into the match arrays in the reference's output order."""
+    dist = np.asarray(dist, np.float32)
+    if len(dist) == 0:
+        return np.zeros(0, np.int64), 0
+    order = np.argsort(dist, kind="stable")
+    if distance_threshold is None:
+        distance_threshold = np.median(dist.astype(np.float64)) * 2.0
+    n_keep = int(np.count_nonzero(dist[order].astype(np.float64) < distance_threshold))
+    return order, n_keep
+
+
+def track_pair(pts1, descriptors1, pts2, descriptors2, camera_matrix, image_shape, ratio_threshold=0.75,
+               threshold_percent=0.02, prob=0.999, threshold=1.0):
+    """tracker.py:214-254 on arrays.
+
+    pts*: float32 [n, 2] keypoint coordinates (level-0 pixels), descriptors*: uint8 [n, 32].
+    Returns a dict: success, query_idx / train_idx / distance (the gated matches in the reference's order,
+    i.e. ascending descriptor distance, stable), E, ransac_mask (uint8 [m], findEssentialMat's), inlier_mask
+    (uint8 [m], after recoverPose's cheirality check), R, t, T (4x4).
+    `success` is False, with the matches still reported, where the reference returns (False, None, None).
+    """
+    from .utils import calculate_essential_matrix, recover_pose
+    out = {"success": False, "E": None, "R": None, "t": None, "T": None, "ransac_mask": None, "inlier_mask": None}
+    q, t, d = match_arrays(descriptors1, descriptors2, ratio_threshold)
+    if len(q):
+        keep = gate_geometric_distance(pts1, pts2, q, t, threshold_percent, image_shape)
+        q, t, d = q[keep], t[keep], d[keep]
+    order, n_keep = gate_descriptor_distance(d)
+    sel = order[:n_keep]
+    q, t, d = q[sel], t[sel], d[sel]
+    out.update(query_idx=q, train_idx=t, distance=d)
+    if len(q) < 8:                                             # tracker.py:233-234
+        return out
+    p1 = np.ascontiguousarray(np.asarray(pts1, np.float32)[q])
+    p2 = np.ascontiguousarray(np.asarray(pts2, np.float32)[t])
+    E, mask = calculate_essential_matrix(p1, p2, camera_matrix, prob=prob, threshold=threshold)
+    if E is None or E.shape != (3, 3):                         # tracker.py:244-245
+        return out
+    out["ransac_mask"] = mask.ravel().copy()
+    _, R, tv, mask = recover_pose(E, p1, p2, camera_matrix, mask=mask)
+    T = np.eye(4)
+    T[:3, :3] = R
+    T[:3, 3] = tv.reshape(3)
+    out.update(success=True, E=E, R=R, t=tv, T=T, inlier_mask=mask.ravel())
+    return out
+
+
+# --------------------------------------------------------------------------- N2: LocalMapper's matcher
+class BFMatcher:
+    """Stand-in for `cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)` (local_mapper.py:116): `knnMatch`
+    with k = 1 or 2 and `match` on the B200 kernels, returning the same tuples of cv2.DMatch."""
+
+    def __init__(self, normType=None, crossCheck=False):
+        import cv2
+        if normType not in (None, cv2.NORM_HAMMING):
+            raise NotImplementedError("only NORM_HAMMING runs on the B200 path")
+        if crossCheck:
+            raise NotImplementedError("crossCheck=True is not used by the reference")
+
+    @staticmethod
+    def _search(query, train):
+        if query is None or train is None or len(query) == 0:
+            return np.zeros((0, 2), np.int32), np.zeros((0, 2), np.int32)
+        if len(train) == 0:
+            n = len(query)
+            return np.full((n, 2), -1, np.int32), np.full((n, 2), -1, np.int32)
+        return _native.bf_knn2_host(np.asarray(query).astype(np.uint8, copy=False),
+                                    np.asarray(train).astype(np.uint8, copy=False))
+
+    def knnMatch(self, queryDescriptors, trainDescriptors, k=2, mask=None, compactResult=False):
+        import cv2
+        if mask is not None or k not in (1, 2):
+            raise NotImplementedError("knnMatch: k in (1, 2) without a mask")
+        idx, dist = self._search(queryDescriptors, trainDescriptors)
+        out = []
+        for r in range(len(idx)):
+            row = tuple(cv2.DMatch(r, int(idx[r, j]), 0, float(dist[r, j])) for j in range(k) if idx[r, j] >= 0)
+            out.append(row)
+        return tuple(out)
+
+    def match(self, queryDescriptors, trainDescriptors, mask=None):
+        return tuple(m[0] for m in self.knnMatch(queryDescriptors, trainDescriptors, k=1, mask=mask) if m)
+
+
+class _Cv2Proxy:
+    """cv2 as seen by an adapted module: BFMatcher and findFundamentalMat(FM_RANSAC) run on the B200
+    kernels, every other attribute is cv2's own."""
+
+    def __init__(self, cv2):
+        self._cv2 = cv2
+
+    def __getattr__(self, name):
+        return getattr(self._cv2, name)
+
+    def BFMatcher(self, normType=None, crossCheck=False):
+        return BFMatcher(normType, crossCheck)
+
+    def findFundamentalMat(self, points1, points2, method=None, ransacReprojThreshold=3.0, confidence=0.99,
+                           maxIters=1000, mask=None):
+        cv2 = self._cv2
+        if method is None:
+            method = cv2.FM_RANSAC
+        n = len(points1)
+        if method != cv2.FM_RANSAC or mask is not None or n < 8:
+            return cv2.findFundamentalMat(points1, points2, method, ransacReprojThreshold, confidence, maxIters)
+        from .utils import find_fundamental_ransac
+        return find_fundamental_ransac(np.asarray(points1, np.float32).reshape(-1, 2),
+                                       np.asarray(points2, np.float32).reshape(-1, 2),
+                                       ransacReprojThreshold, confidence, maxIters)
+
+
+def install_local_mapper_adaptor(module):
+    """Point `module.cv2` (e.g. the reference's `orbslam2.local_mapper`) at the proxy above, so that its
+    private matcher and fundamental-matrix RANSAC use the B200 kernels.  Returns the proxy; undo with
+    `module.cv2 = proxy._cv2`."""
+    import cv2
+    _native.require_gpu()
+    proxy = _Cv2Proxy(cv2)
+    module.cv2 = proxy
+    return proxy
