@@ -58,6 +58,15 @@ def run_gpu_arm(args, rank, world, B):
     b_mcount = torch.zeros(1, dtype=torch.int32, device=dev)
     stream = torch.cuda.current_stream()
     sptr = C.c_void_p(stream.cuda_stream)
+    # "full front-end" workloads add the batched fundamental-matrix RANSAC over every match list of the step
+    ransac = bool(args.ransac) or args.workload == "c3"
+    if ransac:
+        r_F = torch.zeros((B, 9), dtype=torch.float64, device=dev)
+        r_mask = torch.zeros((B, cap), dtype=torch.uint8, device=dev)
+        r_ninl = torch.zeros(B, dtype=torch.int32, device=dev)
+        r_ws = torch.empty(max(int(L.vslam_ransac_fundamental_batched_workspace(B, cap)), 16), dtype=torch.uint8, device=dev)
+        prev_kp = torch.zeros((cap, 6), dtype=torch.float32, device=dev)
+    ransac_events = []
 
     def step(first):
         _native.check(L.vslam_frontend_run(orb.handle, frames.data_ptr(), B, w,
@@ -65,6 +74,28 @@ def run_gpu_arm(args, rank, world, B):
                                            None if first else prev_count.data_ptr(), BN.RATIO,
                                            kp.data_ptr(), desc.data_ptr(), count.data_ptr(),
                                            match.data_ptr(), mcount.data_ptr(), sptr))
+        if ransac:
+            # pairs of this step: (prev, 0) when there is a previous step, then (i, i+1); match row p belongs to
+            # pair p.  Without a previous frame pair 0 is (0, 1) and there are B - 1 pairs.
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            if first:
+                _native.check(L.vslam_ransac_fundamental_batched(
+                    kp.data_ptr(), kp.data_ptr() + cap * 24, cap, match.data_ptr(), mcount.data_ptr(), cap, B - 1,
+                    3.0, 0.99, 1000, C.c_uint64(0x5EED), r_ws.data_ptr(), r_F.data_ptr(), r_mask.data_ptr(),
+                    r_ninl.data_ptr(), sptr))
+            else:
+                _native.check(L.vslam_ransac_fundamental_batched(
+                    prev_kp.data_ptr(), kp.data_ptr(), cap, match.data_ptr(), mcount.data_ptr(), cap, 1,
+                    3.0, 0.99, 1000, C.c_uint64(0x5EED), r_ws.data_ptr(), r_F.data_ptr(), r_mask.data_ptr(),
+                    r_ninl.data_ptr(), sptr))
+                _native.check(L.vslam_ransac_fundamental_batched(
+                    kp.data_ptr(), kp.data_ptr() + cap * 24, cap, match.data_ptr() + cap * 12, mcount.data_ptr() + 4,
+                    cap, B - 1, 3.0, 0.99, 1000, C.c_uint64(0x5EED), r_ws.data_ptr() + 2 * cap * 8,
+                    r_F.data_ptr() + 72, r_mask.data_ptr() + cap, r_ninl.data_ptr() + 4, sptr))
+            ev1.record()
+            ransac_events.append((ev0, ev1))
+            prev_kp.copy_(kp[B - 1], non_blocking=True)
         prev_desc.copy_(desc[B - 1], non_blocking=True)
         prev_count.copy_(count[B - 1:B], non_blocking=True)
 
@@ -135,6 +166,8 @@ def run_gpu_arm(args, rank, world, B):
     value = world * B * K / (ms * 1e-3)
     n_kp = int(count.clamp(max=cap).sum().item())
     n_match = int(mcount.sum().item())
+    ransac_ms = sum(a.elapsed_time(b_) for a, b_ in ransac_events[-K:]) if ransac else 0.0
+    n_inl = int(r_ninl.clamp(min=0).sum().item()) if ransac else None
 
     # ---- e2e through the host-buffer C ABI (pinned host memory, copies timed) -----------
     # Two host threads, each with its own handle (own streams and workspace) and its own pinned result
@@ -252,6 +285,10 @@ def run_gpu_arm(args, rank, world, B):
                          "tensor_frac": pairs_per_s * 512.0 / 4.5e15},
             "kernel_ms_per_step": breakdown,
         }
+        if ransac:
+            breakdown["ransac_f"] = round(ransac_ms / K, 4)
+            line["config"]["ransac"] = "fundamental matrix, thr 3.0, conf 0.99, <= 1000 iterations, every match list"
+            line["config"]["inliers_last_step"] = n_inl
         if world == 1 and not args.no_cpu:
             fps, cores, kind, sample = BN.cpu_front_end_fps(w, h, nf, [host_frames[k] for k in range(min(B, 64))] * 8)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}

@@ -23,6 +23,7 @@
 #ifndef VSLAM_B200_H
 #define VSLAM_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -205,6 +206,24 @@ int vslam_score_essential_host(const double* h_E, const double* h_K, const float
 int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p2, int n, double thr,
                                   double conf, int max_iters, uint64_t seed, double* h_F,
                                   uint8_t* h_mask, int* n_inliers);
+/* Batched, device-resident form of DescriptorMatcher.filter_matches_by_fundamental
+ * (matcher.py:171-200) for the output of vslam_frontend_run: pair p takes its points from
+ * d_match[p] (int32 [pairs][match_capacity][3], d_match_count[p] rows) as
+ * d_kp_query[p * kp_capacity + queryIdx] and d_kp_train[p * kp_capacity + trainIdx]
+ * (for consecutive frames of one keypoint array: d_kp_train = d_kp_query + kp_capacity).
+ * One CTA per pair; pair p gives exactly what vslam_ransac_fundamental_host gives on
+ * its point lists.  Outputs: d_F double [pairs][9], d_mask uint8 [pairs][match_capacity]
+ * (row i <-> match i), d_n_inliers int32 [pairs].  Pairs with fewer than 8 matches
+ * follow matcher.py:184-185: mask rows 1, d_n_inliers = -1, F = 0.  d_workspace:
+ * vslam_ransac_fundamental_batched_workspace(pairs, match_capacity) bytes. */
+size_t vslam_ransac_fundamental_batched_workspace(int pairs, int match_capacity);
+int vslam_ransac_fundamental_batched(const vslam_keypoint* d_kp_query,
+                                     const vslam_keypoint* d_kp_train, int kp_capacity,
+                                     const int32_t* d_match, const int32_t* d_match_count,
+                                     int match_capacity, int pairs, double thr, double conf,
+                                     int max_iters, uint64_t seed, void* d_workspace,
+                                     double* d_F, uint8_t* d_mask, int32_t* d_n_inliers,
+                                     void* stream);
 /* Replaces cv2.findEssentialMat(p1, p2, K, RANSAC, prob, thr) (utils.py:124-125). */
 int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, const double* h_K,
                                 double prob, double thr, int max_iters, uint64_t seed,

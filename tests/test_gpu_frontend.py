@@ -151,3 +151,41 @@ def test_local_mapper_adaptor_reroutes_module_cv2(synth640):
     assert F.shape == (3, 3) and mask.shape == mask_ref.shape and mask.dtype == np.uint8
     a, b = mask.ravel() != 0, mask_ref.ravel() != 0
     assert (a & b).sum() / max((a | b).sum(), 1) >= 0.93 and a.sum() >= 0.97 * b.sum()
+
+
+def test_front_end_full_batched_ransac_equals_per_pair_calls(synth640):
+    """BASELINE config 3 (extract + match + RANSAC-F) in one device-resident call: every pair's F, mask and
+    inlier count equal vslam_ransac_fundamental_host on that pair's point lists bit for bit (same kernel, same
+    seed), the match lists equal the unfused frontend, and the inlier sets meet the cv2 bar of
+    tests/test_gpu_geometry.py."""
+    import cv2
+    from orbslam2 import frontend, utils
+    from orbslam2._native import OrbHandle
+    frames = synth640.frames(0, 6)
+    h = OrbHandle(640, 480, n_features=1000, max_batch=6)
+    out = frontend.front_end_full(h, frames, 0.75, 3.0, 0.99)
+    kp, desc, cnt, match, mc = h.frontend_host(frames, 0.75)
+    assert np.array_equal(out["count"], cnt) and np.array_equal(out["match_count"], mc[:5])
+    for p in range(5):
+        n = int(mc[p])
+        assert n >= 8 and np.array_equal(out["match"][p][:n], match[p][:n])
+        q, t = match[p][:n, 0], match[p][:n, 1]
+        p1 = np.stack([kp[p]["x"][q], kp[p]["y"][q]], axis=1).astype(np.float32)
+        p2 = np.stack([kp[p + 1]["x"][t], kp[p + 1]["y"][t]], axis=1).astype(np.float32)
+        F, mask = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)
+        assert np.array_equal(out["F"][p], F) and np.array_equal(out["mask"][p][:n], mask.ravel())
+        assert int(out["n_inliers"][p]) == int(mask.sum())
+        Fc, mref = cv2.findFundamentalMat(p1, p2, cv2.FM_RANSAC, 3.0, 0.99)
+        a, b = mask.ravel() != 0, mref.ravel() != 0
+        assert (a & b).sum() / max((a | b).sum(), 1) >= 0.93 and a.sum() >= 0.97 * b.sum()
+    h.close()
+    # fewer than 8 matches: matcher.py:184-185 -> all ones, no estimate; no matches at all: nothing set
+    rng = np.random.default_rng(5)
+    noise = rng.integers(0, 256, (2, 240, 320), dtype=np.uint8)
+    noise[1] = 255 - noise[1]
+    h = OrbHandle(320, 240, n_features=300, max_batch=2)
+    out = frontend.front_end_full(h, noise, 0.75, 3.0, 0.99)
+    n = int(out["match_count"][0])
+    if n < 8:
+        assert int(out["n_inliers"][0]) == -1 and out["mask"][0][:n].all() and not out["F"][0].any()
+    h.close()

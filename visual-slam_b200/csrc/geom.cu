@@ -10,8 +10,8 @@
 // K-normalised coordinates; both in double, rounded to float and compared with (float)thr^2.
 // Hypotheses: every RANSAC iteration is one thread (7-point / 5-point minimal solver on a
 // sample drawn from a counter-based generator), every model is scored by one CTA, and the
-// host replays OpenCV's sequential adaptive-termination rule over the per-model inlier counts,
-// so the result is deterministic for a given seed.
+// OpenCV's sequential adaptive-termination rule is replayed over the per-model inlier counts (by one
+// thread of the batched F kernel, on the host for E), so the result is deterministic for a given seed.
 #include <float.h>
 #include <math.h>
 
@@ -217,6 +217,191 @@ int ransac_replay(const std::vector<int>& counts, const std::vector<int>& n_mode
     return best;
 }
 
+// ---- batched, device-resident fundamental-matrix RANSAC: one CTA per frame pair ---------------
+// The CTA gathers the pair's matched points, normalises them (Hartley), then works in rounds of FB_R
+// RANSAC iterations: 7-point hypotheses (one thread each, spread over the warps), inlier counts of the
+// round's models (one warp per model), and the sequential replay of OpenCV's adaptive-termination rule
+// by one thread.  Models past the horizon are never consulted by the replay, so stopping after the round
+// that crosses it gives the same winner as evaluating all max_iters iterations -- at ~95 % inliers the
+// horizon is a handful of iterations and one round is all a pair costs.
+#define FB_R 32                  // iterations per round ...
+#define FB_R0 8                  // ... after a first round of 8: at >= 90 % inliers the horizon is below 8 iterations
+#define FB_THREADS 256
+
+__device__ inline int ransac_update_iters_dev(double p, double ep, int model_points, int max_iters)
+{
+    p = fmax(p, 0.); p = fmin(p, 1.);
+    ep = fmax(ep, 0.); ep = fmin(ep, 1.);
+    double num = fmax(1. - p, DBL_MIN);
+    double denom = 1. - pow(1. - ep, (double)model_points);
+    if (denom < DBL_MIN) return 0;
+    num = log(num);
+    denom = log(denom);
+    return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)llrint(num / denom);
+}
+
+// deterministic block sum (fixed tree), result valid in every thread
+__device__ inline double fb_block_sum(double v, double* s_red)
+{
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0;
+    for (int w = 0; w < FB_THREADS / 32; ++w) t += s_red[w];
+    return t;
+}
+
+__global__ void __launch_bounds__(FB_THREADS)
+vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_keypoint* __restrict__ kp_t, int kp_cap,
+                           const int32_t* __restrict__ match, const int32_t* __restrict__ mcount, int cap,
+                           float thr2, double conf, int max_iters, uint64_t seed, int min_n, float2* __restrict__ ws_pts,
+                           double* __restrict__ out_F, uint8_t* __restrict__ out_mask, int32_t* __restrict__ out_ninl)
+{
+    __shared__ double s_models[FB_R * 3 * 9];
+    __shared__ int s_nm[FB_R], s_counts[FB_R * 3];
+    __shared__ double s_best[9], s_red[FB_THREADS / 32];
+    __shared__ int s_niters, s_maxgood, s_found, s_cnt;
+    const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n = min(mcount ? mcount[pair] : cap, cap);
+    float2* p1 = ws_pts + (size_t)pair * 2 * cap;
+    float2* p2 = p1 + cap;
+    uint8_t* mask = out_mask + (size_t)pair * cap;
+    double* Fo = out_F + (size_t)pair * 9;
+    if (n < min_n) {             // matcher.py:184-185 (min_n = 8): fewer than 8 matches -> (matches, ones), no estimate
+        for (int i = tid; i < n; i += FB_THREADS) mask[i] = 1;
+        if (tid < 9) Fo[tid] = 0.0;
+        if (tid == 0) out_ninl[pair] = -1;
+        return;
+    }
+    // ---- matched points (kp == NULL: the caller placed them in ws_pts)
+    if (match) {
+        const vslam_keypoint* kq = kp_q + (size_t)pair * kp_cap;
+        const vslam_keypoint* kt = kp_t + (size_t)pair * kp_cap;
+        for (int i = tid; i < n; i += FB_THREADS) {
+            const int32_t* m = match + ((size_t)pair * cap + i) * 3;
+            const vslam_keypoint a = kq[m[0]], b = kt[m[1]];
+            p1[i] = make_float2(a.x, a.y);
+            p2[i] = make_float2(b.x, b.y);
+        }
+        __syncthreads();
+    }
+    // ---- Hartley normalisation: centroid, then mean distance to it
+    double sx1 = 0, sy1 = 0, sx2 = 0, sy2 = 0;
+    for (int i = tid; i < n; i += FB_THREADS) {
+        const float2 a = p1[i], b = p2[i];
+        sx1 += a.x; sy1 += a.y; sx2 += b.x; sy2 += b.y;
+    }
+    Norm2 n1, n2;
+    n1.cx = fb_block_sum(sx1, s_red) / n; n1.cy = fb_block_sum(sy1, s_red) / n;
+    n2.cx = fb_block_sum(sx2, s_red) / n; n2.cy = fb_block_sum(sy2, s_red) / n;
+    double d1 = 0, d2 = 0;
+    for (int i = tid; i < n; i += FB_THREADS) {
+        const float2 a = p1[i], b = p2[i];
+        d1 += hypot(a.x - n1.cx, a.y - n1.cy);
+        d2 += hypot(b.x - n2.cx, b.y - n2.cy);
+    }
+    d1 = fb_block_sum(d1, s_red) / n; d2 = fb_block_sum(d2, s_red) / n;
+    n1.s = d1 > 0 ? sqrt(2.0) / d1 : 1.0;
+    n2.s = d2 > 0 ? sqrt(2.0) / d2 : 1.0;
+    if (tid == 0) { s_niters = max_iters; s_maxgood = 0; s_found = 0; }
+    __syncthreads();
+
+    for (int r0 = 0, R = FB_R0; r0 < s_niters; r0 += R, R = FB_R) {
+        // ---- hypotheses of iterations r0 .. r0 + R - 1, one thread each, spread evenly over the warps
+        const int stride = FB_THREADS / R;
+        if (tid % stride == 0) {
+            const int j = tid / stride, it = r0 + j;
+            int kept = 0;
+            if (it < max_iters) {
+                int idx[7];
+                draw_sample<7>(seed, it, n, idx);
+                double x1[7][2], x2[7][2];
+                for (int q = 0; q < 7; ++q) {
+                    const float2 a = p1[idx[q]], b = p2[idx[q]];
+                    x1[q][0] = (a.x - n1.cx) * n1.s; x1[q][1] = (a.y - n1.cy) * n1.s;
+                    x2[q][0] = (b.x - n2.cx) * n2.s; x2[q][1] = (b.y - n2.cy) * n2.s;
+                }
+                double F[3][9];
+                const int nf = solve_7pt(x1, x2, F);
+                for (int k = 0; k < nf; ++k) {
+                    const double* f = F[k];
+                    double A[9], G[9];   // Fn * T1, then T2^T * A  (T = [s 0 -s cx; 0 s -s cy; 0 0 1])
+                    for (int r = 0; r < 3; ++r) {
+                        A[3 * r] = f[3 * r] * n1.s;
+                        A[3 * r + 1] = f[3 * r + 1] * n1.s;
+                        A[3 * r + 2] = f[3 * r + 2] - n1.s * (f[3 * r] * n1.cx + f[3 * r + 1] * n1.cy);
+                    }
+                    for (int c = 0; c < 3; ++c) {
+                        G[c] = n2.s * A[c];
+                        G[3 + c] = n2.s * A[3 + c];
+                        G[6 + c] = A[6 + c] - n2.s * (n2.cx * A[c] + n2.cy * A[3 + c]);
+                    }
+                    bool ok = true;
+                    for (int e = 0; e < 9; ++e) ok &= isfinite(G[e]);
+                    if (!ok) continue;
+                    const double mu = fabs(G[8]) > DBL_EPSILON ? 1.0 / G[8] : 1.0;    // F[2][2] = 1 as OpenCV's run7Point
+                    double* o = s_models + (j * 3 + kept) * 9;
+                    for (int e = 0; e < 9; ++e) o[e] = G[e] * mu;
+                    ++kept;
+                }
+            }
+            s_nm[j] = kept;
+        }
+        __syncthreads();
+        // ---- inlier counts: one warp per model slot
+        for (int slot = wid; slot < R * 3; slot += FB_THREADS / 32) {
+            if (slot % 3 >= s_nm[slot / 3]) continue;
+            const double* M = s_models + slot * 9;
+            int cnt = 0;
+            for (int i = lane; i < n; i += 32) {
+                const float2 a = p1[i], b = p2[i];
+                cnt += f_error(M, a.x, a.y, b.x, b.y) <= thr2;
+            }
+            for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+            if (lane == 0) s_counts[slot] = cnt;
+        }
+        __syncthreads();
+        // ---- OpenCV's sequential loop over this round (cv::RANSACPointSetRegistrator::run)
+        if (tid == 0) {
+            int niters = s_niters, max_good = s_maxgood;
+            for (int j = 0; j < R && r0 + j < niters; ++j)
+                for (int k = 0; k < s_nm[j]; ++k) {
+                    const int good = s_counts[j * 3 + k];
+                    if (good > (max_good > 6 ? max_good : 6)) {
+                        for (int e = 0; e < 9; ++e) s_best[e] = s_models[(j * 3 + k) * 9 + e];
+                        s_found = 1;
+                        max_good = good;
+                        niters = ransac_update_iters_dev(conf, (double)(n - good) / n, 7, niters);
+                    }
+                }
+            s_niters = niters; s_maxgood = max_good;
+        }
+        __syncthreads();
+    }
+    // ---- mask of the winner
+    if (!s_found) {
+        for (int i = tid; i < n; i += FB_THREADS) mask[i] = 0;
+        if (tid < 9) Fo[tid] = 0.0;
+        if (tid == 0) out_ninl[pair] = 0;
+        return;
+    }
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < n; i += FB_THREADS) {
+        const float2 a = p1[i], b = p2[i];
+        const int in = f_error(s_best, a.x, a.y, b.x, b.y) <= thr2;
+        mask[i] = (uint8_t)in;
+        cnt += in;
+    }
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    if (tid < 9) Fo[tid] = s_best[tid];
+    __syncthreads();
+    if (tid == 0) out_ninl[pair] = s_cnt;
+}
+
 }  // namespace
 
 #define GEOM_CUDA(call)                                                                  \
@@ -343,6 +528,31 @@ static int ransac_driver(int mode, const void* d_p1, const void* d_p2, int n, co
     return score_common(mode, h_model, d_p1, d_p2, n, thr2, h_mask, n_inliers);
 }
 
+extern "C" size_t vslam_ransac_fundamental_batched_workspace(int pairs, int cap)
+{
+    return (size_t)(pairs > 0 ? pairs : 0) * 2 * (size_t)(cap > 0 ? cap : 0) * sizeof(float2);
+}
+
+extern "C" int vslam_ransac_fundamental_batched(const vslam_keypoint* d_kp_query, const vslam_keypoint* d_kp_train,
+                                                int kp_capacity, const int32_t* d_match,
+                                                const int32_t* d_match_count, int match_capacity, int pairs,
+                                                double thr, double conf, int max_iters, uint64_t seed,
+                                                void* d_workspace, double* d_F, uint8_t* d_mask,
+                                                int32_t* d_n_inliers, void* stream)
+{
+    VS_REQUIRE(d_kp_query && d_kp_train && d_match && d_match_count && d_workspace && d_F && d_mask && d_n_inliers,
+               "null argument");
+    VS_REQUIRE(pairs >= 0 && match_capacity > 0 && kp_capacity > 0, "bad sizes");
+    VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
+    if (pairs == 0) return VSLAM_OK;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+    vs_ransac_f_batched_kernel<<<pairs, FB_THREADS, 0, (cudaStream_t)stream>>>(
+        d_kp_query, d_kp_train, kp_capacity, d_match, d_match_count, match_capacity, (float)(thr * thr), conf, max_iters,
+        seed, 8, (float2*)d_workspace, d_F, d_mask, d_n_inliers);
+    GEOM_CUDA(cudaGetLastError());
+    return VSLAM_OK;
+}
+
 extern "C" int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p2, int n, double thr, double conf,
                                              int max_iters, uint64_t seed, double* h_F, uint8_t* h_mask,
                                              int* n_inliers)
@@ -350,12 +560,28 @@ extern "C" int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p
     VS_REQUIRE(h_p1 && h_p2 && h_F, "null argument");
     VS_REQUIRE(n >= 7, "need at least 7 correspondences");
     VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
-    DevMem a, b;
-    GEOM_CUDA(a.alloc((size_t)n * 8));
-    GEOM_CUDA(b.alloc((size_t)n * 8));
-    GEOM_CUDA(cudaMemcpy(a.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemcpy(b.p, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
-    return ransac_driver(0, a.p, b.p, n, h_p1, h_p2, (float)(thr * thr), conf, max_iters, seed, h_F, h_mask, n_inliers);
+    // one pair through the batched kernel (same arithmetic, so a batch entry equals a single call)
+    const int cap = n;
+    DevMem pts, F, mask, cnt;
+    GEOM_CUDA(pts.alloc((size_t)2 * cap * sizeof(float2)));
+    GEOM_CUDA(F.alloc(9 * sizeof(double)));
+    GEOM_CUDA(mask.alloc(cap));
+    GEOM_CUDA(cnt.alloc(2 * sizeof(int)));
+    GEOM_CUDA(cudaMemcpy(pts.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(pts.as<float2>() + cap, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    const int n_eff = n;
+    GEOM_CUDA(cudaMemcpy(cnt.as<int>() + 1, &n_eff, sizeof(int), cudaMemcpyHostToDevice));
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+    vs_ransac_f_batched_kernel<<<1, FB_THREADS>>>(nullptr, nullptr, 0, nullptr, cnt.as<int>() + 1, cap, (float)(thr * thr),
+                                                  conf, max_iters, seed, 7, pts.as<float2>(), F.as<double>(),
+                                                  mask.as<uint8_t>(), cnt.as<int>());
+    GEOM_CUDA(cudaGetLastError());
+    int c = 0;
+    GEOM_CUDA(cudaMemcpy(&c, cnt.p, sizeof(int), cudaMemcpyDeviceToHost));
+    GEOM_CUDA(cudaMemcpy(h_F, F.p, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, mask.p, n, cudaMemcpyDeviceToHost));
+    if (n_inliers) *n_inliers = c < 0 ? 0 : c;
+    return VSLAM_OK;
 }
 
 extern "C" int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, const double* h_K,

@@ -105,6 +105,52 @@ def track_pair(pts1, descriptors1, pts2, descriptors2, camera_matrix, image_shap
     return out
 
 
+# --------------------------------------------------------------------------- full front end, batched
+def front_end_full(handle, frames, ratio=0.75, threshold=3.0, confidence=0.99, max_iters=1000, seed=0x5EED):
+    """BASELINE config 3 ("full front-end"): extract every frame, match frame i with i+1, and filter every
+    match list with the fundamental-matrix RANSAC (matcher.py:171-200) -- all on the device, one host
+    round trip.  `handle` is an `_native.OrbHandle`, `frames` uint8 [B, H, W].
+
+    Returns numpy arrays: kp (structured, [B, cap]), desc uint8 [B, cap, 32], count int32 [B],
+    match int32 [B-1, cap, 3], match_count int32 [B-1], F float64 [B-1, 3, 3], mask uint8 [B-1, cap],
+    n_inliers int32 [B-1] (-1: fewer than 8 matches, mask rows all 1 as in matcher.py:184-185).
+    """
+    import ctypes as C
+    import torch
+    _native.require_gpu()
+    L = _native.lib()
+    frames = np.ascontiguousarray(frames, np.uint8)
+    B, h, w = frames.shape
+    cap = handle.kp_capacity
+    dev = torch.device("cuda")
+    d_frames = torch.from_numpy(frames).to(dev)
+    kp = torch.empty((B, cap, 6), dtype=torch.float32, device=dev)
+    desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    count = torch.zeros(B, dtype=torch.int32, device=dev)
+    pairs = max(B - 1, 0)
+    match = torch.empty((max(pairs, 1), cap, 3), dtype=torch.int32, device=dev)
+    mcount = torch.zeros(max(pairs, 1), dtype=torch.int32, device=dev)
+    F = torch.zeros((max(pairs, 1), 9), dtype=torch.float64, device=dev)
+    mask = torch.zeros((max(pairs, 1), cap), dtype=torch.uint8, device=dev)
+    ninl = torch.zeros(max(pairs, 1), dtype=torch.int32, device=dev)
+    ws = torch.empty(max(int(L.vslam_ransac_fundamental_batched_workspace(pairs, cap)), 16), dtype=torch.uint8, device=dev)
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _native.check(L.vslam_frontend_run(handle.handle, d_frames.data_ptr(), B, w, None, None, float(ratio),
+                                       kp.data_ptr(), desc.data_ptr(), count.data_ptr(), match.data_ptr(),
+                                       mcount.data_ptr(), s))
+    if pairs:
+        _native.check(L.vslam_ransac_fundamental_batched(kp.data_ptr(), kp.data_ptr() + cap * 24, cap, match.data_ptr(),
+                                                         mcount.data_ptr(), cap, pairs, float(threshold),
+                                                         float(confidence), int(max_iters), C.c_uint64(seed),
+                                                         ws.data_ptr(), F.data_ptr(), mask.data_ptr(), ninl.data_ptr(), s))
+    torch.cuda.synchronize()
+    kp_np = kp.cpu().numpy().view(_native.KP_DTYPE).reshape(B, cap)
+    return {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy(),
+            "match": match[:pairs].cpu().numpy(), "match_count": mcount[:pairs].cpu().numpy(),
+            "F": F[:pairs].cpu().numpy().reshape(pairs, 3, 3), "mask": mask[:pairs].cpu().numpy(),
+            "n_inliers": ninl[:pairs].cpu().numpy()}
+
+
 # --------------------------------------------------------------------------- N2: LocalMapper's matcher
 class BFMatcher:
     """Stand-in for `cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)` (local_mapper.py:116): `knnMatch`
