@@ -12,17 +12,23 @@
 //   * operands live in shared memory in the canonical K-major no-swizzle UMMA layout (8-row x 16-byte
 //     core matrices; LBO = 128 B between the K halves, SBO = 2048 B between 8-row groups); the bit
 //     expansion writes that layout directly (the k order of a dot product is free, so k = bit index),
-//   * one thread issues 2 x 8 tcgen05.mma (M128 N128 K32, u8 x u8 -> s32) per train tile into one of two
-//     256-column TMEM buffers and commits to an mbarrier,
-//   * all 8 warps expand the next train tile while the tensor core works, then read the finished tile
-//     back with tcgen05.ld 32x32b (thread = TMEM lane = query row, so the top-2 state is private to a
-//     thread and needs no shuffle merge).
+//   * a train set is expanded ONCE (vs_knn2_expand_kernel: operand tile + 16-bit key constants, 33 024 B
+//     per 128 descriptors, L2 resident for the CTAs of the same pair) instead of by every CTA that reads it,
+//   * a producer warp streams those tiles into a 3-stage shared-memory ring with bulk async copies (TMA,
+//     mbarrier complete_tx), issues 2 x 8 tcgen05.mma (M128 N128 K32, u8 x u8 -> s32) per tile into one of
+//     two 256-column TMEM buffers and commits to an mbarrier,
+//   * 16 consumer warps read finished tiles back with tcgen05.ld 32x32b (thread = TMEM lane = query row, so
+//     the top-2 state is private to a thread) and release the TMEM buffer / ring stage through an mbarrier;
+//     there is no CTA-wide barrier in the tile loop.
 #include "common.cuh"
 
 #define T5_ROWS 256          // query rows per CTA
-#define T5_THREADS 512       // 16 warps: warps w and w + 8 read the same TMEM lanes, one column half each
+#define T5_CONSUMERS 512     // 16 warps: warps w and w + 8 read the same TMEM lanes, one column half each
+#define T5_THREADS 544       // + the producer warp
+#define T5_STAGES 3
 #define T5_N 128             // train descriptors per tile
 #define T5_OPER_BYTES 32768  // one 128-row operand tile: 16 groups x 2048 B
+#define T5_TILE_BYTES (T5_OPER_BYTES + 256)   // + the tile's 64 words of 16-bit key constants
 #define T5_INVALID (1023 << 16)   // widened key of a padding column (16-bit key 0xffff)
 
 __device__ __forceinline__ uint32_t t5_expand(uint32_t n) { return (n * 0x00204081u) & 0x01010101u; }
@@ -114,24 +120,59 @@ __device__ __forceinline__ void t5_reduce32(const uint32_t (&v)[32], const uint3
 // 16-bit tile key -> ((distance part) << 16 | train index)
 __device__ __forceinline__ int t5_widen(uint32_t x, int base) { return (int)((x & 0xffc0u) * 1024u + (x & 63u)) + base; }
 
+__device__ __forceinline__ void t5_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n .reg .pred p;\n"
+        "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra D%=;\n bra W%=;\n"
+        "D%=:\n}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+
+// ---- train descriptors -> UMMA operand tiles + key constants (once per train set) ------------------
+// thread = (train row, quarter) with consecutive lanes on consecutive rows; quarter 0 also counts the row's bits
+__global__ void __launch_bounds__(512)
+vs_knn2_expand_kernel(const uint8_t* __restrict__ train, int nt_max, long t_stride, const int32_t* __restrict__ d_nt,
+                      int tiles_max, uint8_t* __restrict__ expanded)
+{
+    const int tile = blockIdx.x, pair = blockIdx.y, tid = threadIdx.x;
+    const int nt = d_nt ? min(d_nt[pair], nt_max) : nt_max;
+    if (tile * T5_N >= nt) return;                       // tiles past the end are never read
+    const uint8_t* tp = train + (size_t)pair * t_stride * 32;
+    uint8_t* out = expanded + ((size_t)pair * tiles_max + tile) * T5_TILE_BYTES;
+    const int row = tid & 127, quarter = tid >> 7, d_idx = tile * T5_N + row;
+    uint2 d = make_uint2(0u, 0u);
+    if (d_idx < nt) d = __ldg((const uint2*)(tp + (size_t)d_idx * 32) + quarter);
+    t5_store_quarter(out, row, quarter, d);
+    if (quarter == 0) {
+        int pb = 0;
+        if (d_idx < nt) {
+            const uint4 x = __ldg((const uint4*)(tp + (size_t)d_idx * 32)), y = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + 1);
+            pb = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
+        }
+        ((uint16_t*)(out + T5_OPER_BYTES))[row] = d_idx < nt ? (uint16_t)(((pb + 256) << 6) | (row & 63)) : (uint16_t)0xffffu;
+    }
+}
+
 __global__ void __launch_bounds__(T5_THREADS, 1)
 vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
-                   const uint8_t* __restrict__ train, int nt_max, long t_stride,
+                   const uint8_t* __restrict__ expanded, int tiles_max, int nt_max,
                    const int32_t* __restrict__ d_nq, const int32_t* __restrict__ d_nt,
                    int nsplit, int4* __restrict__ partial, int32_t* __restrict__ out_idx,
                    int32_t* __restrict__ out_dist)
 {
     extern __shared__ __align__(128) uint8_t t5_smem[];
-    __shared__ __align__(8) unsigned long long s_bar[2];
-    // key constants of a train tile; three deep: a fast warp expands tile i+1 while a slow one still reduces tile i-1
-    __shared__ __align__(16) uint32_t s_c[3][T5_N / 2];   // 16-bit key constants, two columns per word
+    // full[s]: tile landed in ring stage s; done[b]: MMAs into TMEM buffer b finished; free[b]: all 16 consumer
+    // warps are through with TMEM buffer b (and with the ring stage of that tile)
+    __shared__ __align__(8) unsigned long long s_full[T5_STAGES], s_done[2], s_free[2];
     __shared__ uint32_t s_tmem;
     __shared__ int2 s_merge[T5_ROWS];
     const int pair = blockIdx.z, split = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int nq = d_nq ? min(d_nq[pair], nq_max) : nq_max;
     const int nt = d_nt ? min(d_nt[pair], nt_max) : nt_max;
     const int q0 = blockIdx.x * T5_ROWS;
-    const int mtile = (wid >> 2) & 1, chalf = wid >> 3;                  // M-tile and column half this warp reads back
+    const bool consumer = wid < T5_CONSUMERS / 32;
+    const int mtile = (wid >> 2) & 1, chalf = (wid >> 3) & 1;           // M-tile and column half this warp reads back
     const int lrow = mtile * 128 + (wid & 3) * 32 + lane;                // TMEM lane (wid & 3) * 32 + lane of that M-tile
     const int myrow = q0 + lrow;
     if (q0 >= nq) {
@@ -144,9 +185,11 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     }
     uint8_t* sm = t5_smem + ((128u - ((uint32_t)__cvta_generic_to_shared(t5_smem) & 127u)) & 127u);
     uint8_t* sA = sm;                         // 2 x 32 KB: query rows 0..127, 128..255
-    uint8_t* sB = sm + 2 * T5_OPER_BYTES;     // 2 x 32 KB: train tile double buffer
-    const uint32_t sA_u = (uint32_t)__cvta_generic_to_shared(sA), sB_u = (uint32_t)__cvta_generic_to_shared(sB);
-    const uint32_t bar_u = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
+    uint8_t* sT = sm + 2 * T5_OPER_BYTES;     // T5_STAGES x (operand tile + key constants)
+    const uint32_t sA_u = (uint32_t)__cvta_generic_to_shared(sA), sT_u = (uint32_t)__cvta_generic_to_shared(sT);
+    const uint32_t full_u = (uint32_t)__cvta_generic_to_shared(&s_full[0]);
+    const uint32_t done_u = (uint32_t)__cvta_generic_to_shared(&s_done[0]);
+    const uint32_t free_u = (uint32_t)__cvta_generic_to_shared(&s_free[0]);
 
     // ---- TMEM (all 512 columns: two buffers of 2 x 128), barriers
     if (wid == 0) {
@@ -154,112 +197,106 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_u));
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_u + 8));
+        for (int k = 0; k < T5_STAGES; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_u + 8 * k));
+        for (int k = 0; k < 2; ++k) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(done_u + 8 * k));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(free_u + 8 * k), "r"(T5_CONSUMERS / 32));
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // ---- query rows -> A operand, popc(a) of this thread's row
     const uint8_t* qbase = query + (size_t)pair * q_stride * 32;
-    {
+    int pa = 0;
+    if (consumer) {
         const int row = tid & 255, half = tid >> 8;
         const uint4 d = __ldg((const uint4*)(qbase + (size_t)min(q0 + row, nq - 1) * 32) + half);
         t5_store_half(sA + (row >> 7) * T5_OPER_BYTES, row & 127, half, d);
-    }
-    int pa;
-    {
         const uint4* qp = (const uint4*)(qbase + (size_t)min(myrow, nq - 1) * 32);
         const uint4 x = __ldg(qp), y = __ldg(qp + 1);
         pa = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
     }
-    const uint8_t* tp = train + (size_t)pair * t_stride * 32;
     const int tiles = (nt + T5_N - 1) / T5_N;
     const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
+    const int ntile = t_end - t_begin;
 
-    // thread = (train row, quarter) with consecutive lanes on consecutive rows: a quarter-warp's 128-bit stores
-    // cover one 128-byte core-matrix column (conflict-free); quarter 0 reads the whole row for popc(b)
-    auto expand_tile = [&](int tile, int buf, int cbuf) {
-        const int row = tid & 127, quarter = tid >> 7, d_idx = tile * T5_N + row;
-        uint2 d = make_uint2(0u, 0u);
-        if (d_idx < nt) d = __ldg((const uint2*)(tp + (size_t)d_idx * 32) + quarter);
-        t5_store_quarter(sB + buf * T5_OPER_BYTES, row, quarter, d);
-        if (quarter == 0) {
-            int pb = 0;
-            if (d_idx < nt) {
-                const uint4 x = __ldg((const uint4*)(tp + (size_t)d_idx * 32)), y = __ldg((const uint4*)(tp + (size_t)d_idx * 32) + 1);
-                pb = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
-            }
-            ((uint16_t*)s_c[cbuf])[row] = d_idx < nt ? (uint16_t)(((pb + 256) << 6) | (row & 63)) : (uint16_t)0xffffu;
-        }
-    };
-    auto issue_tile = [&](int buf) {                 // one thread: 2 M-tiles x 8 K-steps, then commit to the buffer's barrier
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t idesc = (2u << 4) | ((uint32_t)(T5_N >> 3) << 17) | ((128u >> 4) << 24);   // s32 accum, u8 x u8, K-major both
-#pragma unroll
-        for (int m = 0; m < 2; ++m) {
-            const uint32_t tacc = s_tmem + buf * 256 + m * 128;
-#pragma unroll
-            for (int s = 0; s < 8; ++s) {
-                const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
-                const uint64_t db = t5_smem_desc(sB_u + buf * T5_OPER_BYTES + s * 256);
-                const uint32_t accumulate = s > 0;
-                asm volatile(
-                    "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
-                    " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
-                    ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
-            }
-        }
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_u + 8 * buf) : "memory");
-    };
-
-    int k1 = 0x7fffffff, k2 = 0x7fffffff;       // running pair of widened keys
-    if (t_begin < t_end) expand_tile(t_begin, 0, 0);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = s_tmem;
-    if (tid == 0 && t_begin < t_end) issue_tile(0);
 
-    for (int tile = t_begin; tile < t_end; ++tile) {
-        const int i = tile - t_begin, buf = i & 1;
-        if (tile + 1 < t_end) {
-            expand_tile(tile + 1, buf ^ 1, (i + 1) % 3);          // its previous reader (MMA of tile - 1) completed before the last epilogue
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    int k1 = 0x7fffffff, k2 = 0x7fffffff;       // running pair of widened keys
+    if (!consumer) {
+        // ---- producer: ring loads, MMA issue (one thread)
+        if (lane == 0) {
+            const uint8_t* src = expanded + ((size_t)pair * tiles_max + t_begin) * T5_TILE_BYTES;
+            auto load = [&](int i) {
+                const uint32_t bar = full_u + 8 * (i % T5_STAGES), dst = sT_u + (i % T5_STAGES) * T5_TILE_BYTES;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(T5_TILE_BYTES) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(dst), "l"(src + (size_t)i * T5_TILE_BYTES), "r"(T5_TILE_BYTES), "r"(bar) : "memory");
+            };
+            for (int i = 0; i < T5_STAGES && i < ntile; ++i) load(i);
+            const uint32_t idesc = (2u << 4) | ((uint32_t)(T5_N >> 3) << 17) | ((128u >> 4) << 24);   // s32 accum, u8 x u8, K-major both
+            for (int i = 0; i < ntile; ++i) {
+                const int buf = i & 1;
+                if (i >= 2) {
+                    // epilogue of tile i - 2 is over: its TMEM buffer (this tile's) and its ring stage are free
+                    t5_wait(free_u + 8 * buf, (uint32_t)((i - 2) >> 1) & 1u);
+                    if (i + 1 < ntile && i + 1 >= T5_STAGES) load(i + 1);          // stage (i + 1) % 3 == (i - 2) % 3
+                }
+                t5_wait(full_u + 8 * (i % T5_STAGES), (uint32_t)(i / T5_STAGES) & 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    const uint32_t tacc = tmem + buf * 256 + m * 128;
+#pragma unroll
+                    for (int s = 0; s < 8; ++s) {
+                        const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
+                        const uint64_t db = t5_smem_desc(sT_u + (i % T5_STAGES) * T5_TILE_BYTES + s * 256);
+                        const uint32_t accumulate = s > 0;
+                        asm volatile(
+                            "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                            " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
+                            ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+                    }
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(done_u + 8 * buf) : "memory");
+            }
         }
-        __syncthreads();
-        if (tid == 0 && tile + 1 < t_end) issue_tile(buf ^ 1);
-        // wait for this tile's accumulators
-        {
-            const uint32_t parity = (uint32_t)(i >> 1) & 1u;
-            asm volatile(
-                "{\n .reg .pred p;\n"
-                "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-                " @p bra D%=;\n bra W%=;\n"
-                "D%=:\n}\n" ::"r"(bar_u + 8 * buf), "r"(parity) : "memory");
+    } else {
+        // ---- consumers: finished tiles -> packed top-2 -> running pair
+        for (int i = 0; i < ntile; ++i) {
+            const int buf = i & 1, stage = i % T5_STAGES;
+            t5_wait(full_u + 8 * stage, (uint32_t)(i / T5_STAGES) & 1u);     // the tile's key constants (acquire)
+            t5_wait(done_u + 8 * buf, (uint32_t)(i >> 1) & 1u);              // its accumulators
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + mtile * 128 + chalf * 64;
+            const uint32_t* cbase = (const uint32_t*)(sT + stage * T5_TILE_BYTES + T5_OPER_BYTES) + chalf * 32;
+            // this warp's 64 columns as two 32-column chunks, the second load in flight while the first is reduced
+            uint32_t va[32], vb[32];
+            uint32_t p1 = 0xffffffffu, p2 = 0xffffffffu;
+            t5_tmem_ld32(va, taddr);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            t5_tmem_ld32(vb, taddr + 32);
+            t5_reduce32(va, cbase, p1, p2);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            t5_reduce32(vb, cbase + 16, p1, p2);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(free_u + 8 * buf) : "memory");
+            // the tile's four survivors (two per lane) join the running pair
+            const int base = (t_begin + i) * T5_N + chalf * 64;
+            t5_top2(k1, k2, t5_widen(p1 & 0xffffu, base), t5_widen(p1 >> 16, base));
+            t5_top2(k1, k2, t5_widen(p2 & 0xffffu, base), t5_widen(p2 >> 16, base));
         }
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + mtile * 128 + chalf * 64;
-        const uint32_t* cbase = &s_c[i % 3][chalf * 32];
-        // this warp's 64 columns as two 32-column chunks, the second load in flight while the first is reduced
-        uint32_t va[32], vb[32];
-        uint32_t p1 = 0xffffffffu, p2 = 0xffffffffu;
-        t5_tmem_ld32(va, taddr);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        t5_tmem_ld32(vb, taddr + 32);
-        t5_reduce32(va, cbase, p1, p2);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        t5_reduce32(vb, cbase + 16, p1, p2);
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        // the tile's four survivors (two per lane) join the running pair
-        const int base = tile * T5_N + chalf * 64;
-        t5_top2(k1, k2, t5_widen(p1 & 0xffffu, base), t5_widen(p1 >> 16, base));
-        t5_top2(k1, k2, t5_widen(p2 & 0xffffu, base), t5_widen(p2 >> 16, base));
     }
     // merge the two column halves (two sorted pairs -> the two smallest of the four keys)
-    if (chalf == 1) s_merge[lrow] = make_int2(k1, k2);
+    if (consumer && chalf == 1) s_merge[lrow] = make_int2(k1, k2);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (wid == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
-    if (chalf == 1) return;
+    if (!consumer || chalf == 1) return;
     {
         const int2 o = s_merge[lrow];
         const int n2 = __vimin3_s32(max(k1, o.x), k2, o.y);
@@ -285,13 +322,20 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     }
 }
 
-#define T5_DYN_SMEM (4 * T5_OPER_BYTES + 128)
+#define T5_DYN_SMEM (2 * T5_OPER_BYTES + T5_STAGES * T5_TILE_BYTES + 128)
 
 int vs_knn2_tc5_configure()
 {
     static int done = 0;
     if (!done) {
         VS_CUDA(cudaFuncSetAttribute(vs_knn2_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T5_DYN_SMEM));
+        // the expanded train tiles live in stream-ordered allocations: keep freed blocks in the pool
+        cudaMemPool_t pool;
+        int dev = 0;
+        VS_CUDA(cudaGetDevice(&dev));
+        VS_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+        unsigned long long keep = ~0ull;
+        VS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
         done = 1;
     }
     return VSLAM_OK;
@@ -303,7 +347,15 @@ int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t*
 {
     int rc = vs_knn2_tc5_configure();
     if (rc) return rc;
+    const int tiles_max = (nt + T5_N - 1) / T5_N;
+    uint8_t* expanded = nullptr;
+    if (tiles_max > 0) {                                           // an empty train set has nothing to expand
+        VS_CUDA(cudaMallocAsync((void**)&expanded, (size_t)pairs * tiles_max * T5_TILE_BYTES, s));
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);    // the caller counts the search kernel
+        vs_knn2_expand_kernel<<<dim3(tiles_max, pairs), 512, 0, s>>>(d_t, nt, t_stride, d_nt, tiles_max, expanded);
+    }
     vs_knn2_tc5_kernel<<<dim3((nq + T5_ROWS - 1) / T5_ROWS, nsplit, pairs), T5_THREADS, T5_DYN_SMEM, s>>>(
-        d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, nsplit, partial, d_idx, d_dist);
+        d_q, nq, q_stride, expanded, tiles_max, nt, d_nq, d_nt, nsplit, partial, d_idx, d_dist);
+    if (expanded) VS_CUDA(cudaFreeAsync(expanded, s));
     return VSLAM_OK;
 }
