@@ -8,6 +8,7 @@ hdr = rows[1]; data = rows[2:]
 iS, iE = hdr.index('Source'), hdr.index('Instructions Executed')
 c = collections.Counter()
 for k, r in enumerate(data):
+    if len(r) <= iE or not r[iE].isdigit(): continue
     if not (lo <= k < hi): continue
     t = r[iS].strip().split()
     op = t[1] if t[0].startswith('@') else t[0]

@@ -240,7 +240,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __shared__ int s_n, s_base;
     __shared__ uint32_t s_tx[RAW_W], s_ty[RAW_H];
     __shared__ __align__(8) unsigned long long s_mbar;   // TMA completion barrier (levels >= 1)
-    extern __shared__ __align__(16) uint8_t s_dyn[];   // parent region + horizontal pass (levels >= 1)
+    extern __shared__ __align__(16) uint8_t s_dyn[];   // parent region + vertical pass (levels >= 1)
 
     const VsLevel& L = plan.lv[level];
     const int tid = threadIdx.x;
@@ -301,7 +301,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         // dynamic smem: [par_h][par_w] parent pixels (128-byte aligned for TMA), then the horizontal pass
         // (offset arithmetic on s_dyn, not on a generic address, so that the accesses stay LDS/STS)
         uint8_t* s_par = s_dyn + ((128u - ((uint32_t)__cvta_generic_to_shared(s_dyn) & 127u)) & 127u);
-        uint16_t* s_h = (uint16_t*)(s_par + (size_t)plan.par_h * PW);   // [par_h][RAW_W]
+        uint16_t* s_v = (uint16_t*)(s_par + (size_t)plan.par_h * PW);   // [RAW_H][par_w] vertical pass (8.8 fixed point)
         // bounding box of the parent pixels this tile reads (host-computed per tile column / row)
         const uint32_t bx = __ldg(tab + L.bndx_off + blockIdx.x), by = __ldg(tab + L.bndy_off + blockIdx.y);
         const int px_lo = (int)(bx & 0xffff), px_hi = (int)(bx >> 16), py0 = (int)(by & 0xffff);
@@ -366,33 +366,44 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 " @p bra D%=;\n bra W%=;\n"
                 "D%=:\n}\n" ::"r"(bar) : "memory");
         }
-        // separable INTER_LINEAR_EXACT: thread = one column pair x every 7th row, so that the table
-        // entries are loop invariant.  A column with i0 = sw-1 has weight 0 on its right neighbour,
-        // whatever that byte is.
-        const int cp = tid % (RAW_W / 2), rg7 = tid / (RAW_W / 2);       // 36 column pairs x 7 row groups
-        uint32_t* s_h32 = (uint32_t*)s_h;
-        if (rg7 < 7) {
-            const uint32_t ea = s_tx[2 * cp], eb = s_tx[2 * cp + 1];
-            const int ia = (int)(ea & 0xffff) - pxa, ib = (int)(eb & 0xffff) - pxa;
-            const uint32_t aa = ea >> 16, ab = eb >> 16;
-            for (int r = rg7; r < nrows; r += 7) {
-                const uint8_t* p = s_par + r * PW;
-                const uint32_t ha = (uint32_t)p[ia] * (256 - aa) + (uint32_t)p[ia + 1] * aa;
-                const uint32_t hb = (uint32_t)p[ib] * (256 - ab) + (uint32_t)p[ib + 1] * ab;
-                s_h32[r * (RAW_W / 2) + cp] = ha | (hb << 16);
+        // separable INTER_LINEAR_EXACT, vertical pass first (the weights are exact integers, so the order of
+        // the two passes does not change the result).  Vertical: thread = one output row x every 6th parent
+        // word; four bytes of parent rows j0 / j1 are widened to 16-bit lanes and blended two at a time --
+        // a lane holds at most 255 * 256, so the packed multiply-adds cannot carry between lanes.
+        {
+            const int row = tid / 6, w0 = tid - 6 * row;
+            if (row < RAW_H) {
+                const uint32_t e = s_ty[row];
+                const int j0 = (int)(e & 0xffff);
+                const uint32_t bq = e >> 16, wq = 256u - bq;
+                const int j1 = min(j0 + 1, sh - 1);
+                const uint32_t* pa = (const uint32_t*)(s_par + (j0 - py0) * PW);
+                const uint32_t* pb = (const uint32_t*)(s_par + (j1 - py0) * PW);
+                uint2* dst = (uint2*)(s_v + row * PW);
+                const int nwords = min((px_hi + 1 - pxa) / 4 + 1, PW >> 2);
+#pragma unroll 4
+                for (int wc = w0; wc < nwords; wc += 6) {
+                    const uint32_t ua = pa[wc], ub = pb[wc];
+                    const uint32_t lo = __byte_perm(ua, 0, 0x4140) * wq + __byte_perm(ub, 0, 0x4140) * bq;
+                    const uint32_t hi = __byte_perm(ua, 0, 0x4342) * wq + __byte_perm(ub, 0, 0x4342) * bq;
+                    dst[wc] = make_uint2(lo, hi);
+                }
             }
         }
         __syncthreads();
+        // Horizontal: thread = one column pair x every 7th row, so that the table entries are loop invariant.
+        // A column with i0 = sw-1 has weight 0 on its right neighbour, whatever that value is.
+        const int cp = tid % (RAW_W / 2), rg7 = tid / (RAW_W / 2);       // 36 column pairs x 7 row groups
         if (rg7 < 7) {
+            const uint32_t ea = s_tx[2 * cp], eb = s_tx[2 * cp + 1];
+            const int ia = (int)(ea & 0xffff) - pxa, ib = (int)(eb & 0xffff) - pxa;
+            const uint32_t aa = ea >> 16, ab = eb >> 16, wa = 256u - aa, wb = 256u - ab;
             uint32_t* s_raw32 = (uint32_t*)s_raw;
+#pragma unroll 2
             for (int r = rg7; r < RAW_H; r += 7) {
-                const uint32_t e = s_ty[r];
-                const int j0 = (int)(e & 0xffff);
-                const uint32_t bq = e >> 16;
-                const int j1 = min(j0 + 1, sh - 1);
-                const uint32_t h0 = s_h32[(j0 - py0) * (RAW_W / 2) + cp], h1 = s_h32[(j1 - py0) * (RAW_W / 2) + cp];
-                const uint32_t lo = (h0 & 0xffff) * (256 - bq) + (h1 & 0xffff) * bq + 32768u;
-                const uint32_t hi = (h0 >> 16) * (256 - bq) + (h1 >> 16) * bq + 32768u;
+                const uint16_t* v = s_v + r * PW;
+                const uint32_t lo = (uint32_t)v[ia] * wa + (uint32_t)v[ia + 1] * aa + 32768u;
+                const uint32_t hi = (uint32_t)v[ib] * wb + (uint32_t)v[ib + 1] * ab + 32768u;
                 s_raw32[r * (RAW_S / 2) + cp] = (lo >> 16) | (hi & 0xffff0000u);
             }
         }
@@ -516,39 +527,41 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     }
     __syncthreads();
 
-    // ---- 5. non-max suppression (strict >, non-corners count as 0) + 31-px border -> tile list + histogram
-    for (int i = tid; i < VS_TH * (VS_TW / 4); i += 256) {
-        const int w = i & 15, ty = i >> 4;
-        // words of the score row around the 4 pixels: W1 = (tx-2, tx-1), W2 = (p0, p1), W3 = (p2, p3), W4 = (tx+4, tx+5)
-        const uint16_t* q = s_sc + (ty + 1) * SC_S + 4 * w;
-        const uint2 cm = *(const uint2*)(q + 4);
-        if ((cm.x | cm.y) == 0) continue;
-        const int gy = y0 + ty;
-        if (gy < VS_EDGE || gy >= H - VS_EDGE) continue;
-        const uint32_t m1 = *(const uint32_t*)(q + 2), m4 = *(const uint32_t*)(q + 8);
-        const uint2 cu = *(const uint2*)(q - SC_S + 4), cd = *(const uint2*)(q + SC_S + 4);
-        const uint32_t u1 = *(const uint32_t*)(q - SC_S + 2), u4 = *(const uint32_t*)(q - SC_S + 8);
-        const uint32_t d1 = *(const uint32_t*)(q + SC_S + 2), d4 = *(const uint32_t*)(q + SC_S + 8);
-        // per lane: max of the 8 neighbours; pair A = (p0, p1), pair B = (p2, p3)
-        const uint32_t um = fsr16(cu.x, cu.y), dm = fsr16(cd.x, cd.y), mm = fsr16(cm.x, cm.y);
-        const uint32_t nbA = __vimax3_u16x2(__vimax3_u16x2(fsr16(u1, cu.x), cu.x, um), __vimax3_u16x2(fsr16(d1, cd.x), cd.x, dm),
-                                            __vmaxu2(fsr16(m1, cm.x), mm));
-        const uint32_t nbB = __vimax3_u16x2(__vimax3_u16x2(um, cu.y, fsr16(cu.y, u4)), __vimax3_u16x2(dm, cd.y, fsr16(cd.y, d4)),
-                                            __vmaxu2(mm, fsr16(cm.y, m4)));
-        // bit 15 of a lane of (c + 0x7fff - nb) is set iff c > nb (no carry between lanes: both < 256)
-        const uint32_t kA = ((cm.x + 0x7fff7fffu) - nbA) & 0x80008000u, kB = ((cm.y + 0x7fff7fffu) - nbB) & 0x80008000u;
-        if ((kA | kB) == 0) continue;
+    // ---- 5. non-max suppression (strict >, non-corners count as 0) + 31-px border -> tile list + histogram.
+    // Only queued pairs can hold a score, so the queue is walked again instead of the whole tile: word wi of
+    // score row r and its eight neighbouring words give the 3x3 neighbourhoods of both pixels at once.
+    {
+        const int nqueue = s_nq;
+        for (int qi = tid; qi < nqueue; qi += 256) {
+            const int e = s_queue[qi], r = e >> 6, wi = e & 63;
+            if (r == 0 || r == SC_H - 1 || wi < 2 || wi > VS_TW / 2 + 1) continue;   // ring: neighbours only
+            const uint32_t* q = (const uint32_t*)(s_sc + r * SC_S) + wi;
+            const uint32_t cm = q[0];
+            if (cm == 0) continue;
+            const int gy = y0 - 1 + r;
+            if (gy < VS_EDGE || gy >= H - VS_EDGE) continue;
+            const int SW = SC_S / 2;
+            const uint32_t ml = q[-1], mr = q[1], ul = q[-SW - 1], uc = q[-SW], ur = q[-SW + 1],
+                           dl = q[SW - 1], dc = q[SW], dr = q[SW + 1];
+            // lanes = (left pixel, right pixel) of the pair; fsr16(l, c) = their left neighbours, fsr16(c, r) = right
+            const uint32_t nb = __vimax3_u16x2(__vimax3_u16x2(fsr16(ul, uc), uc, fsr16(uc, ur)),
+                                               __vimax3_u16x2(fsr16(dl, dc), dc, fsr16(dc, dr)),
+                                               __vmaxu2(fsr16(ml, cm), fsr16(cm, mr)));
+            // bit 15 of a lane of (c + 0x7fff - nb) is set iff c > nb (no carry between lanes: both < 256)
+            const uint32_t kk = ((cm + 0x7fff7fffu) - nb) & 0x80008000u;
+            if (kk == 0) continue;
+            const int gx0 = x0 - VS_HALO + 2 * wi;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t kk = j < 2 ? kA : kB, cc = j < 2 ? cm.x : cm.y;
-            const int gx = x0 + 4 * w + j;
-            if (!(kk & ((j & 1) ? 0x80000000u : 0x8000u)) || gx < VS_EDGE || gx >= W - VS_EDGE) continue;
-            const int score = (int)((j & 1) ? (cc >> 16) : (cc & 0xffff)) + thr - 1;
-            const int slot = atomicAdd(&s_n, 1);
-            VsCand c;
-            c.x = (uint16_t)gx; c.y = (uint16_t)gy; c.v = (uint32_t)score;
-            s_list[slot] = c;
-            atomicAdd(&s_hist[score], 1u);
+            for (int j = 0; j < 2; ++j) {
+                const int gx = gx0 + j;
+                if (!(kk & (j ? 0x80000000u : 0x8000u)) || gx < VS_EDGE || gx >= W - VS_EDGE) continue;
+                const int score = (int)(j ? (cm >> 16) : (cm & 0xffff)) + thr - 1;
+                const int slot = atomicAdd(&s_n, 1);
+                VsCand c;
+                c.x = (uint16_t)gx; c.y = (uint16_t)gy; c.v = (uint32_t)score;
+                s_list[slot] = c;
+                atomicAdd(&s_hist[score], 1u);
+            }
         }
     }
     __syncthreads();
@@ -583,7 +596,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
 
 size_t vs_level_dyn_smem(const VsPlan& p)
 {
-    return 128 + (size_t)p.par_h * p.par_w + (size_t)p.par_h * RAW_W * sizeof(uint16_t);
+    return 128 + (size_t)p.par_h * p.par_w + (size_t)RAW_H * p.par_w * sizeof(uint16_t);
 }
 
 int vs_configure_level_smem(const VsPlan& p)
