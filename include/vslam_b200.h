@@ -233,6 +233,32 @@ int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, con
 int vslam_recover_pose_host(const double* h_E, const float* h_p1, const float* h_p2, int n,
                             const double* h_K, uint8_t* h_mask_inout, double* h_R, double* h_t,
                             int* n_good);
+/* Batched, device-resident form of the reference's per-frame tracking step
+ * (Tracker._track_frame, tracker.py:214-254) for the output of vslam_frontend_run: pair p
+ * takes its match list d_match[p] (layout as above) through
+ *   filter_matches_by_geometric_distance(threshold_percent, (image_height, image_width))   matcher.py:109-142
+ *   filter_matches_by_distance()   (stable sort by distance, keep < 2 x median)          matcher.py:144-169
+ *   fewer than 8 left -> failure                                                          tracker.py:233
+ *   cv2.findEssentialMat(p1, p2, K, RANSAC, prob, thr)                                    tracker.py:242
+ *   cv2.recoverPose(E, p1, p2, K, mask)                                                   tracker.py:249
+ * One CTA per pair; the RANSAC and pose stages give what vslam_ransac_essential_host /
+ * vslam_recover_pose_host give on the gated point lists.  Outputs per pair: d_track_match
+ * int32 [match_capacity][3] + d_track_count (the gated matches in the reference's order,
+ * ascending distance, stable), d_E double [9], d_ransac_mask / d_pose_mask uint8
+ * [match_capacity] (row i <-> gated match i), d_R double [9], d_t double [3], d_status
+ * int32 [4] = {1 ok | 0 fewer than 8 gated matches | -1 no essential matrix, points passing
+ * the cheirality check, RANSAC inliers, displacement decisions within 1e-9 of the limit
+ * (non-zero: the caller re-decides that pair on the host with math.hypot)}.  h_K double [9]
+ * row-major (host).  d_workspace: vslam_track_batched_workspace(pairs, match_capacity) bytes. */
+size_t vslam_track_batched_workspace(int pairs, int match_capacity);
+int vslam_track_batched(const vslam_keypoint* d_kp_query, const vslam_keypoint* d_kp_train,
+                        int kp_capacity, const int32_t* d_match, const int32_t* d_match_count,
+                        int match_capacity, int pairs, const double* h_K, int image_width,
+                        int image_height, double threshold_percent, double prob, double thr,
+                        int max_iters, uint64_t seed, void* d_workspace, int32_t* d_track_match,
+                        int32_t* d_track_count, double* d_E, uint8_t* d_ransac_mask,
+                        uint8_t* d_pose_mask, double* d_R, double* d_t, int32_t* d_status,
+                        void* stream);
 /* Replaces cv2.triangulatePoints(P1, P2, p1.T, p2.T) (utils.py:59): per-point DLT.
  * h_X float [4][n] (row-major, un-normalised homogeneous, as cv2 returns it). */
 int vslam_triangulate_host(const double* h_P1, const double* h_P2, const float* h_p1,

@@ -189,3 +189,61 @@ def test_front_end_full_batched_ransac_equals_per_pair_calls(synth640):
     if n < 8:
         assert int(out["n_inliers"][0]) == -1 and out["mask"][0][:n].all() and not out["F"][0].any()
     h.close()
+
+
+def test_track_batched_equals_track_pair_and_reference_gates(synth640):
+    """SURVEY.md 8(f) N1 as one device pipeline: vslam_track_batched (both gates, 5-point RANSAC, recoverPose;
+    one CTA per frame pair) gives, for every pair, exactly what the array-level `track_pair` gives -- the
+    gated match list is also compared with the reference's cv2-object sequence (tracker.py:214-230), E / masks /
+    R / t with the host calls on the same point lists bit for bit (same sampler, solver, error function)."""
+    import cv2
+    from orbslam2 import frontend
+    from orbslam2._native import OrbHandle
+    frames = synth640.frames(0, 6)
+    h = OrbHandle(640, 480, n_features=2000, max_batch=6)
+    out = frontend.track_batched(h, frames, K_SYNTH)
+    kp, desc, cnt = out["kp"], out["desc"], out["count"]
+    assert out["success"].all() and not out["status"][:, 3].any()
+    for p in range(5):
+        n0, n1 = int(cnt[p]), int(cnt[p + 1])
+        pts0 = np.stack([kp[p]["x"][:n0], kp[p]["y"][:n0]], 1).astype(np.float32)
+        pts1 = np.stack([kp[p + 1]["x"][:n1], kp[p + 1]["y"][:n1]], 1).astype(np.float32)
+        ref = frontend.track_pair(pts0, desc[p, :n0], pts1, desc[p + 1, :n1], K_SYNTH, frames[0].shape)
+        m = int(out["track_count"][p])
+        assert m == len(ref["query_idx"]) and m >= 8
+        assert np.array_equal(out["track_match"][p, :m, 0], ref["query_idx"])
+        assert np.array_equal(out["track_match"][p, :m, 1], ref["train_idx"])
+        assert np.array_equal(out["track_match"][p, :m, 2], ref["distance"].astype(np.int32))
+        assert ref["success"]
+        assert np.array_equal(out["E"][p], ref["E"])
+        assert np.array_equal(out["ransac_mask"][p, :m], ref["ransac_mask"])
+        assert np.array_equal(out["inlier_mask"][p, :m], ref["inlier_mask"])
+        assert np.array_equal(out["R"][p], ref["R"]) and np.array_equal(out["t"][p], ref["t"])
+        assert np.array_equal(out["T"][p], ref["T"])
+        assert int(out["status"][p, 2]) == int(ref["ransac_mask"].sum())
+        assert int(out["status"][p, 1]) == int(ref["inlier_mask"].sum())
+        if p == 0:      # the reference's own objects for one pair
+            kps0 = [cv2.KeyPoint(float(x), float(y), 31) for x, y in pts0]
+            kps1 = [cv2.KeyPoint(float(x), float(y), 31) for x, y in pts1]
+            gates = _reference_gates(cv2, kps0, kps1, desc[p, :n0], desc[p + 1, :n1], frames[0].shape)
+            assert [[g.queryIdx, g.trainIdx, int(g.distance)] for g in gates] == out["track_match"][p, :m].tolist()
+    h.close()
+    # degenerate batches: identical frames (all distances 0 -> `<` keeps none -> failure), noise (few matches)
+    same = np.stack([frames[0], frames[0]])
+    h = OrbHandle(640, 480, n_features=500, max_batch=2)
+    out = frontend.track_batched(h, same, K_SYNTH)
+    assert not out["success"][0] and int(out["track_count"][0]) == 0 and int(out["status"][0, 0]) == 0
+    h.close()
+    rng = np.random.default_rng(5)
+    noise = rng.integers(0, 256, (2, 240, 320), dtype=np.uint8)
+    noise[1] = 255 - noise[1]
+    h = OrbHandle(320, 240, n_features=300, max_batch=2)
+    out = frontend.track_batched(h, noise, K_SYNTH)
+    n0, n1 = int(out["count"][0]), int(out["count"][1])
+    pts0 = np.stack([out["kp"][0]["x"][:n0], out["kp"][0]["y"][:n0]], 1).astype(np.float32)
+    pts1 = np.stack([out["kp"][1]["x"][:n1], out["kp"][1]["y"][:n1]], 1).astype(np.float32)
+    ref = frontend.track_pair(pts0, out["desc"][0, :n0], pts1, out["desc"][1, :n1], K_SYNTH, (240, 320))
+    m = int(out["track_count"][0])
+    assert m == len(ref["query_idx"]) and bool(out["success"][0]) == bool(ref["success"])
+    assert np.array_equal(out["track_match"][0, :m, 0], ref["query_idx"])
+    h.close()

@@ -54,6 +54,10 @@ def lib():
         L.vslam_ransac_fundamental_batched_workspace.argtypes = [i32, i32]
         L.vslam_ransac_fundamental_batched_workspace.restype = C.c_size_t
         L.vslam_ransac_fundamental_batched.argtypes = [vp, vp, i32, vp, vp, i32, i32, f64, f64, i32, C.c_uint64, vp, vp, vp, vp, vp]
+        L.vslam_track_batched_workspace.argtypes = [i32, i32]
+        L.vslam_track_batched_workspace.restype = C.c_size_t
+        L.vslam_track_batched.argtypes = [vp, vp, i32, vp, vp, i32, i32, vp, i32, i32, f64, f64, f64, i32, C.c_uint64,
+                                          vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.vslam_frontend_run.argtypes = [vp, vp, i32, i32, vp, vp, f64, vp, vp, vp, vp, vp, vp]
         L.vslam_frontend_run_host.argtypes = [vp, vp, i32, f64, vp, vp, vp, vp, vp]
         L.vslam_orb_set_profiling.argtypes = [vp, i32]

@@ -151,6 +151,91 @@ def front_end_full(handle, frames, ratio=0.75, threshold=3.0, confidence=0.99, m
             "n_inliers": ninl[:pairs].cpu().numpy()}
 
 
+def track_batched(handle, frames, camera_matrix, ratio=0.75, threshold_percent=0.02, prob=0.999, threshold=1.0,
+                  max_iters=1000, seed=None):
+    """The reference's tracking step (tracker.py:214-254) for every consecutive frame pair of `frames`
+    (uint8 [B, H, W]) in two launches after the extraction: kNN-2 + ratio (vslam_frontend_run), then
+    vslam_track_batched (both gates, 5-point RANSAC, recoverPose -- one CTA per pair).  Pair p equals
+    `track_pair` on frames p, p+1; a pair whose displacement gate had a decision within 1e-9 of the limit is
+    re-run through `track_pair` (math.hypot on the host), which has not happened on any test input.
+
+    Returns numpy arrays: kp, desc, count as `front_end_full`; track_match int32 [B-1, cap, 3] /
+    track_count int32 [B-1] (gated matches, ascending distance, stable); E, R float64 [B-1, 3, 3];
+    t float64 [B-1, 3, 1]; T float64 [B-1, 4, 4]; ransac_mask, inlier_mask uint8 [B-1, cap];
+    success bool [B-1]; status int32 [B-1, 4] (include/vslam_b200.h)."""
+    import ctypes as C
+    import torch
+    from .utils import DEFAULT_SEED
+    _native.require_gpu()
+    L = _native.lib()
+    if seed is None:
+        seed = DEFAULT_SEED
+    frames = np.ascontiguousarray(frames, np.uint8)
+    B, h, w = frames.shape
+    cap = handle.kp_capacity
+    dev = torch.device("cuda")
+    d_frames = torch.from_numpy(frames).to(dev)
+    kp = torch.empty((B, cap, 6), dtype=torch.float32, device=dev)
+    desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    count = torch.zeros(B, dtype=torch.int32, device=dev)
+    pairs = max(B - 1, 0)
+    P = max(pairs, 1)
+    match = torch.empty((P, cap, 3), dtype=torch.int32, device=dev)
+    mcount = torch.zeros(P, dtype=torch.int32, device=dev)
+    tmatch = torch.zeros((P, cap, 3), dtype=torch.int32, device=dev)
+    tcount = torch.zeros(P, dtype=torch.int32, device=dev)
+    E = torch.zeros((P, 9), dtype=torch.float64, device=dev)
+    R = torch.zeros((P, 9), dtype=torch.float64, device=dev)
+    t = torch.zeros((P, 3), dtype=torch.float64, device=dev)
+    rmask = torch.zeros((P, cap), dtype=torch.uint8, device=dev)
+    pmask = torch.zeros((P, cap), dtype=torch.uint8, device=dev)
+    status = torch.zeros((P, 4), dtype=torch.int32, device=dev)
+    ws = torch.empty(max(int(L.vslam_track_batched_workspace(pairs, cap)), 16), dtype=torch.uint8, device=dev)
+    K = np.ascontiguousarray(camera_matrix, np.float64).reshape(3, 3)
+    s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _native.check(L.vslam_frontend_run(handle.handle, d_frames.data_ptr(), B, w, None, None, float(ratio),
+                                       kp.data_ptr(), desc.data_ptr(), count.data_ptr(), match.data_ptr(),
+                                       mcount.data_ptr(), s))
+    if pairs:
+        _native.check(L.vslam_track_batched(kp.data_ptr(), kp.data_ptr() + cap * 24, cap, match.data_ptr(),
+                                            mcount.data_ptr(), cap, pairs, _native.ptr(K), w, h,
+                                            float(threshold_percent), float(prob), float(threshold), int(max_iters),
+                                            C.c_uint64(seed), ws.data_ptr(), tmatch.data_ptr(), tcount.data_ptr(),
+                                            E.data_ptr(), rmask.data_ptr(), pmask.data_ptr(), R.data_ptr(),
+                                            t.data_ptr(), status.data_ptr(), s))
+    torch.cuda.synchronize()
+    kp_np = kp.cpu().numpy().view(_native.KP_DTYPE).reshape(B, cap)
+    out = {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy(),
+           "track_match": tmatch[:pairs].cpu().numpy(), "track_count": tcount[:pairs].cpu().numpy(),
+           "E": E[:pairs].cpu().numpy().reshape(pairs, 3, 3), "R": R[:pairs].cpu().numpy().reshape(pairs, 3, 3),
+           "t": t[:pairs].cpu().numpy().reshape(pairs, 3, 1), "ransac_mask": rmask[:pairs].cpu().numpy(),
+           "inlier_mask": pmask[:pairs].cpu().numpy(), "status": status[:pairs].cpu().numpy()}
+    out["success"] = out["status"][:, 0] == 1 if pairs else np.zeros(0, bool)
+    T = np.tile(np.eye(4), (pairs, 1, 1))
+    if pairs:
+        T[:, :3, :3] = out["R"]
+        T[:, :3, 3] = out["t"][:, :, 0]
+    out["T"] = T
+    # borderline displacement decisions: the host's math.hypot decides (matcher.py:138)
+    for p in np.nonzero(out["status"][:, 3] > 0)[0] if pairs else []:
+        n0, n1 = int(out["count"][p]), int(out["count"][p + 1])
+        pts0 = np.stack([kp_np[p]["x"][:n0], kp_np[p]["y"][:n0]], 1)
+        pts1 = np.stack([kp_np[p + 1]["x"][:n1], kp_np[p + 1]["y"][:n1]], 1)
+        r = track_pair(pts0, out["desc"][p, :n0], pts1, out["desc"][p + 1, :n1], K, (h, w), ratio, threshold_percent,
+                       prob, threshold)
+        m = len(r["query_idx"])
+        out["track_count"][p] = m
+        out["track_match"][p, :m, 0] = r["query_idx"]
+        out["track_match"][p, :m, 1] = r["train_idx"]
+        out["track_match"][p, :m, 2] = r["distance"].astype(np.int32)
+        out["success"][p] = r["success"]
+        if r["success"]:
+            out["E"][p], out["R"][p], out["t"][p], out["T"][p] = r["E"], r["R"], r["t"], r["T"]
+            out["ransac_mask"][p, :m] = r["ransac_mask"]
+            out["inlier_mask"][p, :m] = r["inlier_mask"]
+    return out
+
+
 # --------------------------------------------------------------------------- N2: LocalMapper's matcher
 class BFMatcher:
     """Stand-in for `cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)` (local_mapper.py:116): `knnMatch`
