@@ -67,6 +67,31 @@ def run_gpu_arm(args, rank, world, B):
         r_ws = torch.empty(max(int(L.vslam_ransac_fundamental_batched_workspace(B, cap)), 16), dtype=torch.uint8, device=dev)
         prev_kp = torch.zeros((cap, 6), dtype=torch.float32, device=dev)
     ransac_events = []
+    # --track: the reference's tracking step (tracker.py:214-254: both gates, E-RANSAC, recoverPose) on every pair
+    track = bool(getattr(args, "track", False))
+    if track:
+        t_match = torch.zeros((B, cap, 3), dtype=torch.int32, device=dev)
+        t_count = torch.zeros(B, dtype=torch.int32, device=dev)
+        t_E = torch.zeros((B, 9), dtype=torch.float64, device=dev)
+        t_R = torch.zeros((B, 9), dtype=torch.float64, device=dev)
+        t_t = torch.zeros((B, 3), dtype=torch.float64, device=dev)
+        t_rmask = torch.zeros((B, cap), dtype=torch.uint8, device=dev)
+        t_pmask = torch.zeros((B, cap), dtype=torch.uint8, device=dev)
+        t_status = torch.zeros((B, 4), dtype=torch.int32, device=dev)
+        t_ws = torch.empty(max(int(L.vslam_track_batched_workspace(B, cap)), 16), dtype=torch.uint8, device=dev)
+        t_K = np.array([[0.5 * w, 0, 0.5 * w], [0, 0.5 * w, 0.5 * h], [0, 0, 1]], np.float64)
+        if not ransac:
+            prev_kp = torch.zeros((cap, 6), dtype=torch.float32, device=dev)
+    track_events = []
+
+    def track_call(kq, kt, m_off, pairs, o):
+        """pairs frame pairs starting at match row m_off; outputs at row o"""
+        _native.check(L.vslam_track_batched(
+            kq, kt, cap, match.data_ptr() + m_off * cap * 12, mcount.data_ptr() + m_off * 4, cap, pairs,
+            _native.ptr(t_K), w, h, 0.02, 0.999, 1.0, 1000, C.c_uint64(0x5EED), t_ws.data_ptr(),
+            t_match.data_ptr() + o * cap * 12, t_count.data_ptr() + o * 4, t_E.data_ptr() + o * 72,
+            t_rmask.data_ptr() + o * cap, t_pmask.data_ptr() + o * cap, t_R.data_ptr() + o * 72,
+            t_t.data_ptr() + o * 24, t_status.data_ptr() + o * 16, sptr))
 
     def step(first):
         _native.check(L.vslam_frontend_run(orb.handle, frames.data_ptr(), B, w,
@@ -95,6 +120,17 @@ def run_gpu_arm(args, rank, world, B):
                     r_F.data_ptr() + 72, r_mask.data_ptr() + cap, r_ninl.data_ptr() + 4, sptr))
             ev1.record()
             ransac_events.append((ev0, ev1))
+        if track:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            if first:
+                track_call(kp.data_ptr(), kp.data_ptr() + cap * 24, 0, B - 1, 0)
+            else:
+                track_call(prev_kp.data_ptr(), kp.data_ptr(), 0, 1, 0)
+                track_call(kp.data_ptr(), kp.data_ptr() + cap * 24, 1, B - 1, 1)
+            ev1.record()
+            track_events.append((ev0, ev1))
+        if ransac or track:
             prev_kp.copy_(kp[B - 1], non_blocking=True)
         prev_desc.copy_(desc[B - 1], non_blocking=True)
         prev_count.copy_(count[B - 1:B], non_blocking=True)
@@ -168,6 +204,7 @@ def run_gpu_arm(args, rank, world, B):
     n_match = int(mcount.sum().item())
     ransac_ms = sum(a.elapsed_time(b_) for a, b_ in ransac_events[-K:]) if ransac else 0.0
     n_inl = int(r_ninl.clamp(min=0).sum().item()) if ransac else None
+    track_ms = sum(a.elapsed_time(b_) for a, b_ in track_events[-K:]) if track else 0.0
 
     # ---- e2e through the host-buffer C ABI (pinned host memory, copies timed) -----------
     # Two host threads, each with its own handle (own streams and workspace) and its own pinned result
@@ -289,6 +326,14 @@ def run_gpu_arm(args, rank, world, B):
             breakdown["ransac_f"] = round(ransac_ms / K, 4)
             line["config"]["ransac"] = "fundamental matrix, thr 3.0, conf 0.99, <= 1000 iterations, every match list"
             line["config"]["inliers_last_step"] = n_inl
+        if track:
+            breakdown["track"] = round(track_ms / K, 4)
+            st = t_status.cpu().numpy()
+            line["config"]["track"] = ("tracker.py:214-254 per pair: displacement gate 0.02, 2 x median distance gate, "
+                                       "findEssentialMat(RANSAC, 0.999, 1.0), recoverPose")
+            line["config"]["track_last_step"] = {"pairs_ok": int((st[:, 0] == 1).sum()),
+                                                 "gated_matches": int(t_count.sum().item()),
+                                                 "ransac_inliers": int(st[:, 2].sum()), "pose_inliers": int(st[:, 1].sum())}
         if world == 1 and not args.no_cpu:
             fps, cores, kind, sample = BN.cpu_front_end_fps(w, h, nf, [host_frames[k] for k in range(min(B, 64))] * 8)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}

@@ -25,69 +25,113 @@ VS_HD inline void pmul(const double* a, int da, const double* b, int db, double*
         for (int j = 0; j <= db; ++j) out[i + j] += a[i] * b[j];
 }
 
-// Real roots of a degree-10 polynomial (ascending coefficients c[0..10]) by Durand-Kerner in
-// complex double followed by Newton polishing of the near-real roots.  Returns the count.
+VS_HD inline double poly_eval(const double* q, int n, double x)
+{
+    double f = q[n];
+    for (int i = n - 1; i >= 0; --i) f = f * x + q[i];
+    return f;
+}
+
+// The single root of q (degree n) in a bracket [xl, xh] over which q is monotone and changes sign; `up`: q
+// increases through the root.  Newton from the midpoint, bisection whenever a step leaves the bracket.
+VS_HD inline double poly_root_in(const double* q, int n, double xl, double xh, bool up, double tol)
+{
+    double x = 0.5 * (xl + xh);
+    for (int it = 0; it < 80; ++it) {
+        double f = q[n], fp = 0.0;
+        for (int i = n - 1; i >= 0; --i) { fp = fp * x + f; f = f * x + q[i]; }
+        if (f == 0.0) break;
+        if ((f < 0.0) == up) xl = x; else xh = x;
+        double xn = x - f / fp;
+        if (!(xn > xl && xn < xh)) xn = 0.5 * (xl + xh);
+        const double dx = fabs(xn - x);
+        x = xn;
+        if (dx <= tol * (1.0 + fabs(x)) || xh - xl <= tol * (1.0 + fabs(x))) break;
+    }
+    return x;
+}
+
+// Real roots of a degree-10 polynomial (ascending coefficients c[0..10]).  Between two consecutive real roots of
+// p' the polynomial p is monotone, so the real roots of p are bracketed by the real roots of p'; the same holds
+// for p' and p'', ... down to the linear 9th derivative.  Each bracket with a sign change holds exactly one
+// root; the two unbounded outer intervals are searched by doubling steps away from the outermost critical point
+// (the sign at infinity says whether a root is there).  Only real arithmetic, no start values, and the cost
+// follows the number of real roots (typically 2-6) -- the complex Durand-Kerner iteration this replaces spent
+// ~1600 instructions per sweep on all ten roots and often ran into its sweep limit.
 VS_HD inline int real_roots_deg10(const double* c, double* roots)
 {
     const int N = 10;
-    double lead = c[N];
     double mx = 0.0;
     for (int i = 0; i <= N; ++i) mx = fmax(mx, fabs(c[i]));
-    if (!(mx > 0.0) || fabs(lead) < 1e-13 * mx) return 0;
+    if (!(mx > 0.0) || fabs(c[N]) < 1e-13 * mx) return 0;
     double a[N + 1];
-    for (int i = 0; i <= N; ++i) a[i] = c[i] / lead;
-    // Cauchy bound for the starting radius
-    double rad = 0.0;
-    for (int i = 0; i < N; ++i) rad = fmax(rad, fabs(a[i]));
-    rad = fmin(1.0 + rad, 1e6);
-    double zr[N], zi[N];
-    for (int k = 0; k < N; ++k) {
-        double ang = 2.0 * 3.14159265358979323846 * k / N + 0.4;
-        zr[k] = 0.5 * rad * cos(ang) * (0.3 + 0.7 * (k + 1) / N);
-        zi[k] = 0.5 * rad * sin(ang) * (0.3 + 0.7 * (k + 1) / N);
-    }
-    for (int it = 0; it < 120; ++it) {
-        double maxd = 0.0;
-        for (int k = 0; k < N; ++k) {
-            // p(z_k) by Horner
-            double pr = 1.0, pi = 0.0;
-            for (int i = N - 1; i >= 0; --i) {
-                double tr = pr * zr[k] - pi * zi[k] + a[i];
-                pi = pr * zi[k] + pi * zr[k];
-                pr = tr;
-            }
-            // q = prod_{j != k} (z_k - z_j)
-            double qr = 1.0, qi = 0.0;
-            for (int j = 0; j < N; ++j) {
-                if (j == k) continue;
-                double dr = zr[k] - zr[j], di = zi[k] - zi[j];
-                double tr = qr * dr - qi * di;
-                qi = qr * di + qi * dr;
-                qr = tr;
-            }
-            double den = qr * qr + qi * qi;
-            if (den < 1e-300) den = 1e-300;
-            double dr = (pr * qr + pi * qi) / den, di = (pi * qr - pr * qi) / den;
-            zr[k] -= dr;
-            zi[k] -= di;
-            maxd = fmax(maxd, fabs(dr) + fabs(di));
+    for (int i = 0; i <= N; ++i) a[i] = c[i] / c[N];
+    double B = 0.0;
+    for (int i = 0; i < N; ++i) B = fmax(B, fabs(a[i]));
+    B = fmin(1.0 + B, 1e8);                         // Cauchy bound; an essential matrix from |z| > 1e8 is degenerate anyway
+    double crit[N], next[N];
+    int nc = 0;                                     // real roots of the derivative one level up, ascending
+    for (int m = N - 1; m >= 0; --m) {              // level m: q = m-th derivative (up to a positive factor), degree n
+        const int n = N - m;
+        double q[N + 1];
+        for (int i = 0; i <= n; ++i) {
+            double f = a[i + m];
+            for (int k = 0; k < m; ++k) f *= (double)(i + m - k);   // (i+m)! / i!
+            q[i] = f;
         }
-        if (maxd < 1e-14 * rad) break;
-    }
-    int n = 0;
-    for (int k = 0; k < N; ++k) {
-        if (fabs(zi[k]) > 1e-5 * (1.0 + fabs(zr[k]))) continue;
-        double x = zr[k];
-        for (int it = 0; it < 4; ++it) {          // Newton on the real polynomial
-            double f = a[N], fp = 0.0;
-            for (int i = N - 1; i >= 0; --i) { fp = fp * x + f; f = f * x + a[i]; }
-            if (fp != 0.0 && isfinite(f / fp)) x -= f / fp;
+        const double tol = m == 0 ? 4e-16 : 1e-11;
+        int nr = 0;
+        // (-inf, first anchor): q(-inf) has the sign (-1)^n (q's leading coefficient is positive)
+        const double a0 = nc > 0 ? crit[0] : 0.0;
+        double fprev = poly_eval(q, n, a0);
+        {
+            const bool neg_inf_negative = (n & 1) != 0;
+            if (fprev != 0.0 && ((fprev < 0.0) != neg_inf_negative)) {
+                double h = 0.25 * (1.0 + fabs(a0)), xin = a0;
+                for (int it = 0; it < 64; ++it, h *= 2.0) {
+                    const double xo = a0 - h;
+                    if ((poly_eval(q, n, xo) < 0.0) == neg_inf_negative) { next[nr++] = poly_root_in(q, n, xo, xin, neg_inf_negative, tol); break; }
+                    xin = xo;
+                    if (h > 2.0 * B) break;
+                }
+            } else if (fprev == 0.0 && nc == 0) {
+                next[nr++] = a0;
+            }
         }
+        // between consecutive critical points
+        for (int iv = 0; iv < nc; ++iv) {
+            const double lo = crit[iv], hi = iv + 1 < nc ? crit[iv + 1] : 0.0;
+            if (fprev == 0.0) next[nr++] = lo;       // a critical point that is itself a root
+            if (iv + 1 == nc) break;
+            const double fhi = poly_eval(q, n, hi);
+            if (hi > lo && fprev != 0.0 && fhi != 0.0 && ((fprev < 0.0) != (fhi < 0.0)))
+                next[nr++] = poly_root_in(q, n, lo, hi, fprev < 0.0, tol);
+            fprev = fhi;
+        }
+        // (last anchor, +inf): q(+inf) > 0
+        {
+            const double a1 = nc > 0 ? crit[nc - 1] : 0.0;
+            if (fprev < 0.0) {
+                double h = 0.25 * (1.0 + fabs(a1)), xin = a1;
+                for (int it = 0; it < 64; ++it, h *= 2.0) {
+                    const double xo = a1 + h;
+                    if (poly_eval(q, n, xo) > 0.0) { next[nr++] = poly_root_in(q, n, xin, xo, true, tol); break; }
+                    xin = xo;
+                    if (h > 2.0 * B) break;
+                }
+            }
+        }
+        nc = nr;
+        for (int i = 0; i < nr; ++i) crit[i] = next[i];
+    }
+    int nout = 0;
+    for (int k = 0; k < nc; ++k) {
+        const double x = crit[k];
         bool dup = false;
-        for (int j = 0; j < n; ++j) dup |= fabs(roots[j] - x) < 1e-9 * (1.0 + fabs(x));
-        if (!dup && isfinite(x)) roots[n++] = x;
+        for (int j = 0; j < nout; ++j) dup |= fabs(roots[j] - x) < 1e-9 * (1.0 + fabs(x));
+        if (!dup && isfinite(x)) roots[nout++] = x;
     }
-    return n;
+    return nout;
 }
 
 // 5-point solver.  x1, x2: 5 correspondences in normalised camera coordinates.

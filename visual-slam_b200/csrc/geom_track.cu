@@ -26,8 +26,12 @@
 #include "geom_ransac.cuh"
 #include "geom_pose.cuh"
 
-#define TK_THREADS 256
-#define TK_R 32                  // RANSAC iterations per round (the 0.999 horizon at 95 % inliers is 27)
+#define TK_THREADS 128
+#define TK_R 32                  // RANSAC iterations per round ...
+#define TK_R0 8                  // ... after a first round of 8 (the 0.999 horizon is 5 iterations at 95 % inliers, 8 at 90 %)
+#ifndef TK_CTAS
+#define TK_CTAS 3                // resident CTAs per SM the register budget is capped for
+#endif
 
 namespace {
 
@@ -40,7 +44,7 @@ struct TrackParams {
     uint64_t seed;
 };
 
-__global__ void __launch_bounds__(TK_THREADS)
+__global__ void __launch_bounds__(TK_THREADS, TK_CTAS)
 vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_keypoint* __restrict__ kp_t, int kp_cap,
                         const int32_t* __restrict__ match, const int32_t* __restrict__ mcount, int cap,
                         const TrackParams P, int32_t* __restrict__ ws_list, double2* __restrict__ ws_pts,
@@ -154,10 +158,12 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
     __syncthreads();
 
     // ---- D. RANSAC rounds
-    for (int r0 = 0; r0 < s_niters; r0 += TK_R) {
-        const int stride = TK_THREADS / TK_R;
-        if (tid % stride == 0) {
-            const int j = tid / stride, it = r0 + j;
+    // The minimal samples of a round are the lanes of warp 0 (the solver is one long double-precision chain per
+    // sample: packed into one warp it costs one instruction stream per round instead of one per warp; the other
+    // warps wait at the barrier and the SM's other CTAs fill the issue slots).
+    for (int r0 = 0, R = TK_R0; r0 < s_niters; r0 += R, R = TK_R) {
+        if (tid < R) {
+            const int j = tid, it = r0 + j;
             int ne = 0;
             if (it < P.max_iters) {
                 int idx[5];
@@ -175,7 +181,7 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
             s_nm[j] = ne;
         }
         __syncthreads();
-        for (int slot = wid; slot < TK_R * 10; slot += TK_THREADS / 32) {
+        for (int slot = wid; slot < R * 10; slot += TK_THREADS / 32) {
             if (slot % 10 >= s_nm[slot / 10]) continue;
             const double* M = s_models + slot * 9;
             int cnt = 0;
@@ -189,7 +195,7 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
         __syncthreads();
         if (tid == 0) {       // cv::RANSACPointSetRegistrator::run over this round, model_points = 5
             int niters = s_niters, max_good = s_maxgood;
-            for (int j = 0; j < TK_R && r0 + j < niters; ++j)
+            for (int j = 0; j < R && r0 + j < niters; ++j)
                 for (int k = 0; k < s_nm[j]; ++k) {
                     const int good = s_counts[j * 10 + k];
                     if (good > (max_good > 4 ? max_good : 4)) {
