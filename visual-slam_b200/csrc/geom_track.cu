@@ -30,7 +30,7 @@
 #define TK_R 32                  // RANSAC iterations per round ...
 #define TK_R0 8                  // ... after a first round of 8 (the 0.999 horizon is 5 iterations at 95 % inliers, 8 at 90 %)
 #ifndef TK_CTAS
-#define TK_CTAS 3                // resident CTAs per SM the register budget is capped for
+#define TK_CTAS 4                // resident CTAs per SM the register budget is capped for
 #endif
 
 namespace {
