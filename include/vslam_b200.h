@@ -75,6 +75,16 @@ typedef struct vslam_orb vslam_orb;
 
 int vslam_orb_create(const vslam_orb_params* params, vslam_orb** out);
 int vslam_orb_destroy(vslam_orb* orb);
+/* Keypoint distribution of the detector.  VSLAM_DIST_CV2_ORB (default) is what the
+ * reference runs: cv2.ORB's per-level retain-best by Harris response (extractor.py:38-48).
+ * VSLAM_DIST_ORBSLAM2 gives `ini_threshold` (extractor.py:34, stored and unused by the
+ * reference) the meaning it has in ORB-SLAM2: per 30-px cell FAST at ini_threshold with
+ * fallback to min_threshold, quadtree distribution to the level quota, response = FAST
+ * score.  The reference holds no implementation of it (parity unpinned, see
+ * oracle/orbslam2_oracle.py); pyramid, blur, orientation and rBRIEF are shared. */
+#define VSLAM_DIST_CV2_ORB 0
+#define VSLAM_DIST_ORBSLAM2 1
+int vslam_orb_set_distribution(vslam_orb* orb, int mode, int ini_threshold);
 /* Effective keypoint capacity per frame and pyramid geometry of a handle. */
 int vslam_orb_kp_capacity(const vslam_orb* orb);
 int vslam_orb_level_info(const vslam_orb* orb, int level, int* w, int* h, int* pitch,

@@ -124,3 +124,28 @@ def test_geometry_scoring_and_pose(name, tag, K):
     ref = g[tag + "_tri_X"]
     assert X.shape == ref.shape
     assert np.allclose(X[:3] / X[3], ref[:3] / ref[3], rtol=2e-3, atol=1e-4)   # float32 output of a 4x4 SVD
+
+
+def test_orbslam2_oracle_invariants():
+    """oracle/orbslam2_oracle.py (parity unpinned: the reference has no such mode): the quadtree keeps one
+    corner per node, never more than quota + 3 nodes once past the first round, all of them when the quota
+    exceeds the corner count; the per-cell rule keeps weak corners only in cells without a strong one."""
+    from oracle import orbslam2_oracle as OS
+    rng = np.random.default_rng(11)
+    pts = rng.permutation(560 * 400)[:3000]
+    rx, ry = (pts % 560).astype(np.int32), (pts // 560).astype(np.int32)
+    sc = rng.integers(7, 120, 3000).astype(np.int32)
+    for n in (1, 5, 100, 434, 2999, 5000):
+        sel = OS.distribute_octree(rx, ry, sc, 560, 400, n)
+        assert len(set(sel)) == len(sel)
+        assert len(sel) <= max(n + 3, 4) and (len(sel) >= min(n, 3000) or n > 3000)
+        if n >= 3000:
+            assert len(sel) == 3000
+    sel = OS.distribute_octree(rx, ry, sc, 560, 400, 434)
+    # every kept corner is the strongest of the corners closer to it than to any other kept one in its node:
+    # cheap necessary check -- the global maximum is always kept
+    assert int(np.argmax(sc)) in sel or sc[sel].max() == sc.max()
+    xs = np.array([40, 45, 100, 300], np.int32); ys = np.array([40, 44, 40, 200], np.int32)
+    ss = np.array([25, 9, 9, 8], np.int32)
+    keep = OS.cell_filter(xs, ys, ss, 640, 480, 20)
+    assert keep.tolist() == [True, False, True, True]

@@ -242,6 +242,23 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     return VSLAM_OK;
 }
 
+extern "C" int vslam_orb_set_distribution(vslam_orb* o, int mode, int ini_threshold)
+{
+    VS_REQUIRE(o, "null handle");
+    VS_REQUIRE(mode == VSLAM_DIST_CV2_ORB || mode == VSLAM_DIST_ORBSLAM2, "unknown distribution mode");
+    if (mode == VSLAM_DIST_ORBSLAM2) {
+        VS_REQUIRE(ini_threshold >= o->prm.fast_threshold && ini_threshold < 255,
+                   "ini_threshold must lie in [min_threshold, 255)");
+        VS_REQUIRE(o->plan.width - 56 <= 4096 && o->plan.height - 56 <= 4096,
+                   "quadtree distribution handles frames up to 4152 px per side");
+        int rc = vs_configure_octree_smem();
+        if (rc) return rc;
+    }
+    o->dist_mode = mode;
+    o->ini_threshold = ini_threshold;
+    return VSLAM_OK;
+}
+
 extern "C" int vslam_orb_kp_capacity(const vslam_orb* o) { return o ? o->plan.kp_cap : VSLAM_E_INVALID; }
 
 extern "C" int vslam_orb_level_info(const vslam_orb* o, int level, int* w, int* h, int* pitch, float* scale,

@@ -101,6 +101,8 @@ struct vslam_orb {
     int32_t* d_match;
     int32_t* d_match_count;
     int frame_pitch;
+    int dist_mode;             // 0: cv2.ORB (Harris retain-best), 1: ORB-SLAM2-style cells + quadtree (orb_octree.cu)
+    int ini_threshold;         // initial FAST threshold of mode 1
     cudaStream_t stream;       // own stream for *_host calls
     // chunked host pipeline (vslam_frontend_run_host): copy-in / copy-out streams and per-chunk events
     cudaStream_t stream_in, stream_out, stream2;   // stream / stream2 alternate between compute chunks
@@ -126,6 +128,8 @@ struct vslam_orb {
 // kernels / launchers implemented in the other translation units
 int vs_configure_level_smem(const VsPlan& p);
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);
+int vs_configure_octree_smem(void);
+int vs_launch_octree(vslam_orb* o, int batch, cudaStream_t s);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
 int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,

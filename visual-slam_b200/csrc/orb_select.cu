@@ -438,17 +438,23 @@ int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
 {
     const VsPlan& p = o->plan;
     const size_t fstride = (size_t)pitch * p.height;
-    vs_prof_mark(o, VS_PROF_HARRIS, s);
-    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    vs_harris_kernel<<<dim3(VS_HARRIS_CTAS, p.n_levels, batch), 256, 0, s>>>(
-        p, d_frames, pitch, fstride, o->d_pyr, o->d_cand, o->d_counters);
-    int max_stage = 0;
-    for (int l = 0; l < p.n_levels; ++l) max_stage = max(max_stage, p.lv[l].stage_cap);
-    size_t smem = (size_t)max_stage * sizeof(unsigned long long);
-    vs_prof_mark(o, VS_PROF_SELECT, s);
-    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    vs_select_kernel<<<dim3(p.n_levels, batch), 256, smem, s>>>(p, o->d_cand, o->d_stage,
-                                                               o->d_counters, o->d_status);
+    if (o->dist_mode == 1) {
+        vs_prof_mark(o, VS_PROF_SELECT, s);
+        int rc = vs_launch_octree(o, batch, s);
+        if (rc) return rc;
+    } else {
+        vs_prof_mark(o, VS_PROF_HARRIS, s);
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+        vs_harris_kernel<<<dim3(VS_HARRIS_CTAS, p.n_levels, batch), 256, 0, s>>>(
+            p, d_frames, pitch, fstride, o->d_pyr, o->d_cand, o->d_counters);
+        int max_stage = 0;
+        for (int l = 0; l < p.n_levels; ++l) max_stage = max(max_stage, p.lv[l].stage_cap);
+        size_t smem = (size_t)max_stage * sizeof(unsigned long long);
+        vs_prof_mark(o, VS_PROF_SELECT, s);
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+        vs_select_kernel<<<dim3(p.n_levels, batch), 256, smem, s>>>(p, o->d_cand, o->d_stage,
+                                                                   o->d_counters, o->d_status);
+    }
     vs_prof_mark(o, VS_PROF_DESCRIBE, s);
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     vs_describe_kernel<<<dim3((p.kp_cap + 8 * VS_DESC_PER_WARP - 1) / (8 * VS_DESC_PER_WARP), batch), 256, 0, s>>>(

@@ -41,6 +41,7 @@ def lib():
         L.vslam_orb_create.argtypes = [C.POINTER(OrbParams), C.POINTER(vp)]
         L.vslam_orb_destroy.argtypes = [vp]
         L.vslam_orb_kp_capacity.argtypes = [vp]
+        L.vslam_orb_set_distribution.argtypes = [vp, i32, i32]
         L.vslam_orb_level_info.argtypes = [vp, i32] + [vp] * 5
         L.vslam_orb_detect_and_compute.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp]
         L.vslam_orb_detect_and_compute_host.argtypes = [vp, vp, i32, vp, vp, vp]
@@ -106,12 +107,18 @@ class OrbHandle:
     """Owns a vslam_orb workspace planned for one frame size."""
 
     def __init__(self, width, height, n_features=2000, scale_factor=1.2, n_levels=8, fast_threshold=7,
-                 max_batch=1, kp_capacity=0):
+                 max_batch=1, kp_capacity=0, distribution="cv2", ini_threshold=20):
+        """distribution: "cv2" = the reference's cv2.ORB retain-best by Harris response (default);
+        "orbslam2" = per-cell ini/min FAST thresholds + quadtree (include/vslam_b200.h, VSLAM_DIST_ORBSLAM2)."""
         require_gpu()
+        if distribution not in ("cv2", "orbslam2"):
+            raise ValueError("unknown distribution %r" % (distribution,))
         self.params = OrbParams(int(width), int(height), int(n_features), int(n_levels), int(fast_threshold),
                                 float(np.float32(scale_factor)), int(max_batch), int(kp_capacity))
         self._h = C.c_void_p()
         check(lib().vslam_orb_create(C.byref(self.params), C.byref(self._h)))
+        if distribution == "orbslam2":
+            check(lib().vslam_orb_set_distribution(self._h, 1, int(ini_threshold)))
         self.kp_capacity = lib().vslam_orb_kp_capacity(self._h)
         self.width, self.height, self.max_batch, self.n_levels = int(width), int(height), int(max_batch), int(n_levels)
 

@@ -19,11 +19,19 @@ def _cv2():
 class ORBExtractor:
     """ORB feature extractor (extractor.py:13-48)."""
 
-    def __init__(self, n_features=2000, scale_factor=1.2, n_levels=8, ini_threshold=20, min_threshold=7):
+    def __init__(self, n_features=2000, scale_factor=1.2, n_levels=8, ini_threshold=20, min_threshold=7,
+                 distribution="cv2"):
+        """The five reference parameters (extractor.py:19-35), plus one opt-in that the reference does not
+        have: distribution="orbslam2" makes `detect_and_compute` spread keypoints the ORB-SLAM2 way (FAST at
+        ini_threshold per 30-px cell with fallback to min_threshold, quadtree to the level quota, response =
+        FAST score) instead of cv2.ORB's Harris retain-best.  The default reproduces the reference."""
+        if distribution not in ("cv2", "orbslam2"):
+            raise ValueError("distribution must be 'cv2' or 'orbslam2'")
+        self.distribution = distribution
         self.n_features = n_features
         self.scale_factor = scale_factor
         self.n_levels = n_levels
-        self.ini_threshold = ini_threshold      # stored and unused, as in the reference (extractor.py:34)
+        self.ini_threshold = ini_threshold      # stored and unused by the reference (extractor.py:34); used by "orbslam2"
         self.min_threshold = min_threshold      # reaches cv2.ORB_create as fastThreshold (extractor.py:47)
         self._handles = {}
 
@@ -35,7 +43,8 @@ class ORBExtractor:
             if len(self._handles) >= 4:          # bound the workspace cache
                 self._handles.pop(next(iter(self._handles))).close()
             hd = _native.OrbHandle(w, h, n_features=key[2], scale_factor=self.scale_factor,
-                                   n_levels=self.n_levels, fast_threshold=self.min_threshold, max_batch=1)
+                                   n_levels=self.n_levels, fast_threshold=self.min_threshold, max_batch=1,
+                                   distribution=self.distribution, ini_threshold=self.ini_threshold)
             self._handles[key] = hd
         return hd
 
@@ -72,7 +81,8 @@ class ORBExtractor:
             # retain-best kept more ties than the default slack: re-run with room for all of them
             big = _native.OrbHandle(w, h, n_features=self.n_features, scale_factor=self.scale_factor,
                                     n_levels=self.n_levels, fast_threshold=self.min_threshold, max_batch=1,
-                                    kp_capacity=n)
+                                    kp_capacity=n, distribution=self.distribution,
+                                    ini_threshold=self.ini_threshold)
             try:
                 kp, desc, cnt = big.detect_and_compute_host(gray)
             finally:
