@@ -232,6 +232,9 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (0 = workload default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--distribution", default="cv2", choices=["cv2", "orbslam2"],
+                    help="keypoint distribution: cv2 = the reference's cv2.ORB retain-best (the metric's config), "
+                         "orbslam2 = ini/min cell thresholds + quadtree (SURVEY 8(f) N4)")
     ap.add_argument("--track", action="store_true", help="add the batched tracking step (gates + E-RANSAC + recoverPose) to every step")
     ap.add_argument("--ransac", action="store_true", help="add the batched RANSAC-F stage to every step (default for c3)")
     args = ap.parse_args()

@@ -38,8 +38,9 @@ def run_gpu_arm(args, rank, world, B):
             host_frames[k] = np.clip(f, 0, 255).astype(np.uint8)
     frames = torch.from_numpy(host_frames).to(dev)
 
+    dist_mode = getattr(args, "distribution", "cv2")
     orb = _native.OrbHandle(w, h, n_features=nf, scale_factor=BN.SCALE, n_levels=BN.N_LEVELS,
-                            fast_threshold=BN.FAST_THR, max_batch=B)
+                            fast_threshold=BN.FAST_THR, max_batch=B, distribution=dist_mode, ini_threshold=20)
     cap = orb.kp_capacity
     kp = torch.empty((B, cap, 6), dtype=torch.float32, device=dev)
     desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
@@ -214,7 +215,8 @@ def run_gpu_arm(args, rank, world, B):
     pin_frames = torch.from_numpy(host_frames).pin_memory()
     n_workers = 2
     handles = [orb, _native.OrbHandle(w, h, n_features=nf, scale_factor=BN.SCALE, n_levels=BN.N_LEVELS,
-                                      fast_threshold=BN.FAST_THR, max_batch=B)]
+                                      fast_threshold=BN.FAST_THR, max_batch=B, distribution=dist_mode,
+                                      ini_threshold=20)]
     outs = []
     for _ in range(n_workers):
         outs.append((torch.empty((B, cap, 6), dtype=torch.float32).pin_memory(),
@@ -326,6 +328,9 @@ def run_gpu_arm(args, rank, world, B):
             breakdown["ransac_f"] = round(ransac_ms / K, 4)
             line["config"]["ransac"] = "fundamental matrix, thr 3.0, conf 0.99, <= 1000 iterations, every match list"
             line["config"]["inliers_last_step"] = n_inl
+        if dist_mode != "cv2":
+            line["config"]["distribution"] = ("orbslam2: FAST ini 20 / min 7 per 30-px cell, quadtree to the level quota "
+                                              "(non-default option; the `select` slot times the quadtree kernel)")
         if track:
             breakdown["track"] = round(track_ms / K, 4)
             st = t_status.cpu().numpy()

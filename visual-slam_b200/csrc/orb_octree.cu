@@ -65,7 +65,7 @@ __device__ __forceinline__ void bitonic_sort_u32_desc(uint32_t* a, int np2, int 
 }
 
 __global__ void __launch_bounds__(OT_THREADS)
-vs_octree_kernel(const __grid_constant__ VsPlan plan, int ini_thr, const VsCand* __restrict__ cand,
+vs_octree_kernel(const __grid_constant__ VsPlan plan, int ini_thr, int m_lo, int m_hi, const VsCand* __restrict__ cand,
                  VsCand* __restrict__ stage, int32_t* __restrict__ counters, int32_t* __restrict__ status)
 {
     extern __shared__ __align__(16) unsigned long long s_key[];      // [np2] (key << 32) | candidate index
@@ -78,6 +78,8 @@ vs_octree_kernel(const __grid_constant__ VsPlan plan, int ini_thr, const VsCand*
     int32_t* ctr = counters + ((size_t)b * plan.n_levels + level) * VS_CTR_STRIDE;
     const int ncand = ctr[VS_CTR_NCAND], N = L.quota;
     if (ncand == 0 || N == 0) return;            // NFINAL stays 0 (counters are zeroed per batch)
+    // one launch per shared-memory size class: this CTA's class is the one whose sort buffer fits its corners
+    if (min(ncand, OT_MAXM) <= m_lo || min(ncand, OT_MAXM) > m_hi) return;
     const VsCand* cl = cand + (size_t)b * plan.cand_frame_entries + L.cand_off;
 
     // ---- geometry of ComputeKeyPointsOctTree with EDGE = 31
@@ -255,11 +257,14 @@ vs_octree_kernel(const __grid_constant__ VsPlan plan, int ini_thr, const VsCand*
 
 }  // namespace
 
-size_t vs_octree_smem(void) { return (size_t)OT_MAXM * (sizeof(unsigned long long) + 2); }
+// shared-memory size classes (corners per level and frame): small levels run several CTAs per SM
+static const int kOctreeClass[] = {0, 2048, 8192, OT_MAXM};
+
+static size_t vs_octree_smem(int m) { return (size_t)m * (sizeof(unsigned long long) + 2); }
 
 int vs_configure_octree_smem(void)
 {
-    VS_CUDA(cudaFuncSetAttribute(vs_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vs_octree_smem()));
+    VS_CUDA(cudaFuncSetAttribute(vs_octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vs_octree_smem(OT_MAXM)));
     return VSLAM_OK;
 }
 
@@ -267,9 +272,14 @@ int vs_configure_octree_smem(void)
 int vs_launch_octree(vslam_orb* o, int batch, cudaStream_t s)
 {
     const VsPlan& p = o->plan;
-    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    vs_octree_kernel<<<dim3(p.n_levels, batch), OT_THREADS, vs_octree_smem(), s>>>(
-        p, o->ini_threshold, o->d_cand, o->d_stage, o->d_counters, o->d_status);
+    int max_cand = 0;
+    for (int l = 0; l < p.n_levels; ++l) max_cand = max(max_cand, p.lv[l].cand_cap);
+    for (int c = 1; c < 4; ++c) {
+        if (kOctreeClass[c - 1] >= max_cand) break;       // no level can hold that many corners
+        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+        vs_octree_kernel<<<dim3(p.n_levels, batch), OT_THREADS, vs_octree_smem(kOctreeClass[c]), s>>>(
+            p, o->ini_threshold, kOctreeClass[c - 1], kOctreeClass[c], o->d_cand, o->d_stage, o->d_counters, o->d_status);
+    }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
 }
