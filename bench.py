@@ -238,6 +238,8 @@ def main():
     ap.add_argument("--track", action="store_true", help="add the batched tracking step (gates + E-RANSAC + recoverPose) to every step")
     ap.add_argument("--ransac", action="store_true", help="add the batched RANSAC-F stage to every step (default for c3)")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: NCCL's version banner / warnings go to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":
