@@ -123,9 +123,10 @@ def test_frontend_host_chunked_pipeline_equals_unfused(oracle):
     h.close(); h1.close()
 
 
-def test_knn2_mma_sync_engine_still_exact(tmp_path):
-    """The default kNN-2 engine is the tcgen05 kernel; the mma.sync int8 kernel stays selectable
-    (VSLAM_KNN=imma, read once per process) and must give the same bit-exact answers."""
+@pytest.mark.parametrize("engine", ["imma", "popc"])
+def test_knn2_mma_sync_engine_still_exact(tmp_path, engine):
+    """The default kNN-2 engine is the tcgen05 kernel; the mma.sync int8 kernel and the XOR + POPC kernel stay
+    selectable (VSLAM_KNN=imma | popc, read once per process) and must give the same bit-exact answers."""
     import os
     import subprocess
     import sys
@@ -141,6 +142,6 @@ def test_knn2_mma_sync_engine_still_exact(tmp_path):
         "    i, d = _native.bf_knn2_host(q, t); ri, rd = O.bf_knn2(q, t)\n"
         "    assert np.array_equal(i, ri) and np.array_equal(d, rd), (nq, nt)\n"
         "print('ok')\n" % (os.path.join(root, "visual-slam_b200"), root))
-    env = dict(os.environ, VSLAM_KNN="imma")
+    env = dict(os.environ, VSLAM_KNN=engine)
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]

@@ -19,10 +19,10 @@ sys.path.insert(0, os.path.join(ROOT, "visual-slam_b200"))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--engine", default="tcgen05", choices=["tcgen05", "imma"])
+    ap.add_argument("--engine", default="tcgen05", choices=["tcgen05", "imma", "popc"])
     args = ap.parse_args()
-    if args.engine == "imma":
-        os.environ["VSLAM_KNN"] = "imma"
+    if args.engine != "tcgen05":
+        os.environ["VSLAM_KNN"] = args.engine
     import torch
     from orbslam2 import _native
     L = _native.lib()

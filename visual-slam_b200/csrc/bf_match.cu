@@ -309,7 +309,18 @@ int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t*
                        int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
 
 // kNN-2 engine for nt <= 65536: 1 = tcgen05 kind::i8 (bf_match_tc5.cu), 0 = mma.sync int8 (above).
-// VSLAM_KNN=imma|tc5 overrides the default.
+// VSLAM_KNN=imma|tc5 overrides the default; VSLAM_KNN=popc forces the XOR + POPC kernel (the formulation
+// BASELINE.json's north_star names) at every size, for the popc-pipe roofline of tools/knn_sweep.py.
+static int knn_force_popc()
+{
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("VSLAM_KNN");
+        mode = (e && !strcmp(e, "popc")) ? 1 : 0;
+    }
+    return mode;
+}
+
 static int knn_use_tc5()
 {
     static int mode = -1;
@@ -330,7 +341,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
                    int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
 {
     if (pairs <= 0 || nq <= 0) return VSLAM_OK;
-    const bool mma = nt <= 65536;  // the tensor-core kernels pack the train index into 16 bits
+    const bool mma = nt <= 65536 && !knn_force_popc();  // the tensor-core kernels pack the train index into 16 bits
     const int qtiles = mma ? (nq + KT_Q - 1) / KT_Q : (nq + BF_THREADS - 1) / BF_THREADS;
     const bool tc5 = mma && knn_use_tc5();
     const int ttiles = tc5 ? (nt + 127) / 128 : mma ? (nt + KT_T - 1) / KT_T : (nt + BF_TILE - 1) / BF_TILE;
