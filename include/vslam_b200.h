@@ -103,6 +103,15 @@ int vslam_orb_detect_and_compute(vslam_orb* orb, const uint8_t* d_frames, int ba
 int vslam_orb_detect_and_compute_host(vslam_orb* orb, const uint8_t* h_frames, int batch,
                                       vslam_keypoint* h_kp, uint8_t* h_desc,
                                       int32_t* h_count);
+/* The same with BGR host frames (uint8 [batch][height][width][3], tightly packed), for callers
+ * that hold colour frames like Tracker.process_frame (tracker.py:84-87): one upload, the
+ * cvtColor(BGR2GRAY) of extractor.py:61-62 runs on the device in front of the pyramid. */
+int vslam_orb_detect_and_compute_host_bgr(vslam_orb* orb, const uint8_t* h_bgr, int batch,
+                                          vslam_keypoint* h_kp, uint8_t* h_desc,
+                                          int32_t* h_count);
+/* cv2.cvtColor(COLOR_BGR2GRAY) on device buffers (d_bgr uint8 [n_pixels][3] -> d_gray uint8
+ * [n_pixels]); bit-exact with OpenCV's fixed-point formula. */
+int vslam_bgr2gray(const uint8_t* d_bgr, size_t n_pixels, uint8_t* d_gray, void* stream);
 /* Status of the last extraction on this handle: VSLAM_OK, or VSLAM_E_CAPACITY when
  * ties at a retain-best cut exceeded the staging capacity (results then differ from
  * the reference).  Synchronises the stream of that call. */

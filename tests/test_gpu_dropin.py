@@ -174,3 +174,35 @@ def test_filter_by_fundamental_and_initializer():
     assert len(pts) >= 20
     vis = init.draw_initialization(g["gray1"], g["gray2"], vm[:50])
     assert isinstance(vis, np.ndarray) and vis.size > 0
+
+
+def test_bgr_frames_ingested_on_device(synth640):
+    """Colour frames (what Tracker.process_frame hands to the extractor, tracker.py:84-87) are uploaded once and
+    converted on the device (K0) in front of the pyramid: same keypoints / descriptors as converting first, and
+    the conversion equals cv2's fixed-point formula on a sweep of colours incl. the unaligned tail."""
+    import cv2
+    from orbslam2 import _native
+    from orbslam2.extractor import ORBExtractor
+    gray = synth640.frame(2)
+    rng = np.random.default_rng(3)
+    bgr = np.stack([np.clip(gray.astype(np.int16) + rng.integers(-40, 41, gray.shape), 0, 255).astype(np.uint8)
+                    for _ in range(3)], axis=2)
+    ref_gray = cv2.cvtColor(bgr, cv2.COLOR_BGR2GRAY)     # type container only elsewhere; here the K0 golden formula
+    ex = ORBExtractor(n_features=1500)
+    k_bgr, d_bgr = ex.detect_and_compute(bgr)
+    k_gray, d_gray = ex.detect_and_compute(ref_gray)
+    assert len(k_bgr) == len(k_gray) and np.array_equal(d_bgr, d_gray)
+    assert [(k.pt, k.angle, k.response, k.octave) for k in k_bgr] == [(k.pt, k.angle, k.response, k.octave) for k in k_gray]
+    # batch of two frames through the handle
+    hd = _native.OrbHandle(640, 480, n_features=1500, max_batch=2)
+    kp2, desc2, cnt2 = hd.detect_and_compute_host_bgr(np.stack([bgr, bgr[:, ::-1].copy()]))
+    kp1, desc1, cnt1 = hd.detect_and_compute_host(np.stack([ref_gray, cv2.cvtColor(bgr[:, ::-1].copy(), cv2.COLOR_BGR2GRAY)]))
+    assert np.array_equal(cnt1, cnt2) and np.array_equal(desc1, desc2) and np.array_equal(kp1, kp2)
+    hd.close()
+    # conversion alone on odd sizes (byte tail) against the formula
+    for h, w in ((7, 13), (1, 1), (33, 31)):
+        c = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        out = np.empty((h, w), np.uint8)
+        _native.check(_native.lib().vslam_bgr2gray_host(_native.ptr(c), h, w, _native.ptr(out)))
+        want = ((c[..., 0].astype(np.int64) * 3735 + c[..., 1].astype(np.int64) * 19235 + c[..., 2].astype(np.int64) * 9798 + 16384) >> 15).astype(np.uint8)
+        assert np.array_equal(out, want) and np.array_equal(out, cv2.cvtColor(c, cv2.COLOR_BGR2GRAY))

@@ -226,7 +226,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     if (!o) return VSLAM_OK;
     cudaDeviceSynchronize();
     void* ptrs[] = {o->d_pyr, o->d_cand, o->d_stage, o->d_counters, o->d_tab, o->d_status, o->d_knn_idx,
-                    o->d_knn_dist, o->d_frames, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
+                    o->d_knn_dist, o->d_frames, o->d_bgr, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
     if (o->stream_in) cudaStreamDestroy(o->stream_in);
@@ -335,6 +335,32 @@ extern "C" int vslam_orb_detect_and_compute_host(vslam_orb* o, const uint8_t* h_
     cudaStream_t s = o->stream;
     const size_t fbytes = (size_t)p.width * p.height;
     VS_CUDA(cudaMemcpyAsync(o->d_frames, h_frames, batch * fbytes, cudaMemcpyHostToDevice, s));
+    rc = vslam_orb_detect_and_compute(o, o->d_frames, batch, p.width, o->d_kp, o->d_desc, o->d_count, s);
+    if (rc) return rc;
+    VS_CUDA(cudaMemcpyAsync(h_kp, o->d_kp, (size_t)batch * p.kp_cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, s));
+    VS_CUDA(cudaMemcpyAsync(h_desc, o->d_desc, (size_t)batch * p.kp_cap * 32, cudaMemcpyDeviceToHost, s));
+    VS_CUDA(cudaMemcpyAsync(h_count, o->d_count, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+    VS_CUDA(cudaStreamSynchronize(s));
+    return vslam_orb_last_status(o);
+}
+
+// Ingest on the device: BGR frames are uploaded once, converted to gray (K0) into the frame staging and
+// extracted from there -- no gray image travels back to the host as with cvtColor + detectAndCompute
+// (extractor.py:61-65).
+extern "C" int vslam_orb_detect_and_compute_host_bgr(vslam_orb* o, const uint8_t* h_bgr, int batch,
+                                                     vslam_keypoint* h_kp, uint8_t* h_desc, int32_t* h_count)
+{
+    VS_REQUIRE(o && h_bgr && h_kp && h_desc && h_count, "null argument");
+    VS_REQUIRE(batch >= 1 && batch <= o->prm.max_batch, "batch exceeds max_batch");
+    int rc = vs_ensure_host_staging(o);
+    if (rc) return rc;
+    const VsPlan& p = o->plan;
+    cudaStream_t s = o->stream;
+    const size_t px = (size_t)p.width * p.height;
+    if (!o->d_bgr) VS_CUDA(cudaMalloc((void**)&o->d_bgr, (size_t)o->prm.max_batch * px * 3 + 256));
+    VS_CUDA(cudaMemcpyAsync(o->d_bgr, h_bgr, batch * px * 3, cudaMemcpyHostToDevice, s));
+    rc = vs_launch_bgr2gray(o->d_bgr, o->d_frames, batch * px, s);
+    if (rc) return rc;
     rc = vslam_orb_detect_and_compute(o, o->d_frames, batch, p.width, o->d_kp, o->d_desc, o->d_count, s);
     if (rc) return rc;
     VS_CUDA(cudaMemcpyAsync(h_kp, o->d_kp, (size_t)batch * p.kp_cap * sizeof(vslam_keypoint), cudaMemcpyDeviceToHost, s));

@@ -95,6 +95,7 @@ struct vslam_orb {
     int32_t* d_knn_dist;
     // host staging for *_host entry points
     uint8_t* d_frames;     // [max_batch][h][pitch0]
+    uint8_t* d_bgr;        // [max_batch][h][w][3] staging of vslam_orb_detect_and_compute_host_bgr (lazy)
     vslam_keypoint* d_kp;
     uint8_t* d_desc;
     int32_t* d_count;
@@ -128,6 +129,7 @@ struct vslam_orb {
 // kernels / launchers implemented in the other translation units
 int vs_configure_level_smem(const VsPlan& p);
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);
+int vs_launch_bgr2gray(const uint8_t* d_bgr, uint8_t* d_gray, size_t n_pixels, cudaStream_t s);
 int vs_configure_octree_smem(void);
 int vs_launch_octree(vslam_orb* o, int batch, cudaStream_t s);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,

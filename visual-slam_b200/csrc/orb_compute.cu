@@ -11,12 +11,44 @@
 
 #include "brief.cuh"
 
-__global__ void vs_bgr2gray_kernel(const uint8_t* __restrict__ bgr, uint8_t* __restrict__ gray, size_t n)
+// four pixels per thread: three aligned 32-bit loads (12 BGR bytes), one 32-bit store
+__global__ void __launch_bounds__(256)
+vs_bgr2gray_kernel(const uint8_t* __restrict__ bgr, uint8_t* __restrict__ gray, size_t n)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;   // pixel quad
+    const size_t i = 4 * q;
     if (i >= n) return;
-    const uint8_t* p = bgr + 3 * i;
-    gray[i] = (uint8_t)((p[0] * 3735 + p[1] * 19235 + p[2] * 9798 + 16384) >> 15);
+    if (i + 4 <= n && ((((size_t)bgr) | ((size_t)gray)) & 3) == 0) {
+        const uint32_t* p = (const uint32_t*)bgr + 3 * q;
+        const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+        // bytes: w0 = B0 G0 R0 B1, w1 = G1 R1 B2 G2, w2 = R2 B3 G3 R3
+        const uint32_t g0 = ((w0 & 255) * 3735 + ((w0 >> 8) & 255) * 19235 + ((w0 >> 16) & 255) * 9798 + 16384) >> 15;
+        const uint32_t g1 = ((w0 >> 24) * 3735 + (w1 & 255) * 19235 + ((w1 >> 8) & 255) * 9798 + 16384) >> 15;
+        const uint32_t g2 = (((w1 >> 16) & 255) * 3735 + (w1 >> 24) * 19235 + (w2 & 255) * 9798 + 16384) >> 15;
+        const uint32_t g3 = (((w2 >> 8) & 255) * 3735 + ((w2 >> 16) & 255) * 19235 + (w2 >> 24) * 9798 + 16384) >> 15;
+        ((uint32_t*)gray)[q] = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+        return;
+    }
+    for (size_t k = i; k < n && k < i + 4; ++k) {
+        const uint8_t* p = bgr + 3 * k;
+        gray[k] = (uint8_t)((p[0] * 3735 + p[1] * 19235 + p[2] * 9798 + 16384) >> 15);
+    }
+}
+
+int vs_launch_bgr2gray(const uint8_t* d_bgr, uint8_t* d_gray, size_t n, cudaStream_t s)
+{
+    if (n == 0) return VSLAM_OK;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+    vs_bgr2gray_kernel<<<(unsigned)((n / 4 + 256) / 256), 256, 0, s>>>(d_bgr, d_gray, n);
+    VS_CUDA(cudaGetLastError());
+    return VSLAM_OK;
+}
+
+// device-pointer form for callers that already hold BGR frames in HBM (e.g. a decoder's output)
+extern "C" int vslam_bgr2gray(const uint8_t* d_bgr, size_t n_pixels, uint8_t* d_gray, void* stream)
+{
+    VS_REQUIRE(d_bgr && d_gray, "null argument");
+    return vs_launch_bgr2gray(d_bgr, d_gray, n_pixels, (cudaStream_t)stream);
 }
 
 extern "C" int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_gray)
@@ -27,11 +59,7 @@ extern "C" int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, 
     VS_CUDA(cudaMalloc(&d_in, 3 * n));
     cudaError_t e = cudaMalloc(&d_out, n);
     if (e == cudaSuccess) e = cudaMemcpy(d_in, h_bgr, 3 * n, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) {
-        __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-        vs_bgr2gray_kernel<<<(unsigned)((n + 255) / 256), 256>>>(d_in, d_out, n);
-        e = cudaGetLastError();
-    }
+    if (e == cudaSuccess && vs_launch_bgr2gray(d_in, d_out, n, 0) != VSLAM_OK) e = cudaErrorLaunchFailure;
     if (e == cudaSuccess) e = cudaMemcpy(h_gray, d_out, n, cudaMemcpyDeviceToHost);
     cudaFree(d_in);
     if (d_out) cudaFree(d_out);

@@ -45,6 +45,8 @@ def lib():
         L.vslam_orb_level_info.argtypes = [vp, i32] + [vp] * 5
         L.vslam_orb_detect_and_compute.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp]
         L.vslam_orb_detect_and_compute_host.argtypes = [vp, vp, i32, vp, vp, vp]
+        L.vslam_orb_detect_and_compute_host_bgr.argtypes = [vp, vp, i32, vp, vp, vp]
+        L.vslam_bgr2gray.argtypes = [vp, C.c_size_t, vp, vp]
         L.vslam_orb_last_status.argtypes = [vp]
         L.vslam_orb_debug_level.argtypes = [vp, i32, i32, i32, vp]
         L.vslam_orb_debug_candidates.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]
@@ -154,6 +156,19 @@ class OrbHandle:
         desc = np.zeros((b, self.kp_capacity, 32), np.uint8)
         cnt = np.zeros(b, np.int32)
         check(lib().vslam_orb_detect_and_compute_host(self._h, ptr(frames), b, ptr(kp), ptr(desc), ptr(cnt)))
+        return kp, desc, cnt
+
+    def detect_and_compute_host_bgr(self, frames_bgr):
+        """frames uint8 [B,H,W,3] (BGR) -> like detect_and_compute_host; the gray conversion runs on the device."""
+        frames_bgr = np.ascontiguousarray(frames_bgr, np.uint8)
+        if frames_bgr.ndim == 3:
+            frames_bgr = frames_bgr[None]
+        b = frames_bgr.shape[0]
+        assert frames_bgr.shape[1:] == (self.height, self.width, 3), frames_bgr.shape
+        kp = np.zeros((b, self.kp_capacity), KP_DTYPE)
+        desc = np.zeros((b, self.kp_capacity, 32), np.uint8)
+        cnt = np.zeros(b, np.int32)
+        check(lib().vslam_orb_detect_and_compute_host_bgr(self._h, ptr(frames_bgr), b, ptr(kp), ptr(desc), ptr(cnt)))
         return kp, desc, cnt
 
     def frontend_host(self, frames, ratio=0.75):

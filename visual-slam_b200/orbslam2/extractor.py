@@ -72,12 +72,22 @@ class ORBExtractor:
     # ---------------------------------------------------------------------- API
     def detect_and_compute(self, image):
         """extractor.py:50-67 -> (tuple of cv2.KeyPoint, uint8 [n, 32]) or ((), None)."""
-        gray = self._gray(image)
-        h, w = gray.shape
-        hd = self._handle(w, h)
-        kp, desc, cnt = hd.detect_and_compute_host(gray)
+        image = np.asarray(image)
+        if image.ndim == 3 and image.shape[2] == 3 and image.dtype == np.uint8:
+            # colour frame: one upload, cvtColor(BGR2GRAY) runs on the device in front of the pyramid
+            h, w = image.shape[:2]
+            hd = self._handle(w, h)
+            kp, desc, cnt = hd.detect_and_compute_host_bgr(image)
+            gray = None
+        else:
+            gray = self._gray(image)
+            h, w = gray.shape
+            hd = self._handle(w, h)
+            kp, desc, cnt = hd.detect_and_compute_host(gray)
         n = int(cnt[0])
         if n > hd.kp_capacity:
+            if gray is None:
+                gray = self._gray(image)
             # retain-best kept more ties than the default slack: re-run with room for all of them
             big = _native.OrbHandle(w, h, n_features=self.n_features, scale_factor=self.scale_factor,
                                     n_levels=self.n_levels, fast_threshold=self.min_threshold, max_batch=1,
