@@ -12,6 +12,8 @@
 // rule); blockIdx.z runs over descriptor-set pairs (consecutive frames of a batch).
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 #ifndef VS_KNN_DEFAULT_TC5
@@ -116,7 +118,7 @@ vs_knn2_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
 // ---------------------------------------------------------------------------
 // Tensor-core variant (nt <= 65536).  Brute-force Hamming matching is a binary GEMM; the POPC
 // pipe issues 16 lanes/clk/SM, which the scalar kernel above already saturates (93 % measured),
-// while the int8 MMA pipe does the same pair 3.8x faster (scratch/ubench/imma.cu: 0.12
+// while the int8 MMA pipe does the same pair 3.8x faster (tools/ubench/imma.cu: 0.12
 // IMMA.16832 per clk per SMSP).  Bits are expanded to 0/1 bytes, so that
 //     dot(a, b) = popc(a & b),   hamming = popc(a) + popc(b) - 2 dot   (exact int32).
 // The k order of a dot product is free: k-step s of a descriptor is its 32-bit word s, thread
@@ -333,8 +335,12 @@ static int knn_use_tc5()
     return mode;
 }
 
+// scratch of the split-train path, shared by every caller of the process: launches that use it are serialised
 static int4* g_partial = nullptr;
 static size_t g_partial_bytes = 0;
+static std::mutex g_partial_mu;
+static cudaEvent_t g_partial_ev = nullptr;     // end of the last launch pair that used the scratch
+static cudaStream_t g_partial_last = nullptr;
 
 int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
                    long t_stride, const int32_t* d_nq, const int32_t* d_nt, int pairs,
@@ -353,13 +359,17 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
         if (nsplit > ttiles) nsplit = ttiles;
         if (nsplit > 64) nsplit = 64;
     }
+    std::unique_lock<std::mutex> lock(g_partial_mu, std::defer_lock);
     if (nsplit > 1) {
+        lock.lock();
         size_t need = (size_t)pairs * nsplit * nq * sizeof(int4);
         if (need > g_partial_bytes) {
             if (g_partial) { VS_CUDA(cudaStreamSynchronize(s)); VS_CUDA(cudaFree(g_partial)); g_partial = nullptr; }
             VS_CUDA(cudaMalloc(&g_partial, need));
             g_partial_bytes = need;
         }
+        // another stream may still be reading / writing the scratch: order this launch behind it
+        if (g_partial_ev && g_partial_last != s) VS_CUDA(cudaStreamWaitEvent(s, g_partial_ev, 0));
     }
     vs_prof_mark(prof, VS_PROF_KNN2, s);
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
@@ -376,6 +386,9 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_knn2_merge_kernel<<<dim3((nq + 255) / 256, pairs), 256, 0, s>>>(g_partial, nq, d_nq, nsplit,
                                                                           d_idx, d_dist);
+        if (!g_partial_ev) VS_CUDA(cudaEventCreateWithFlags(&g_partial_ev, cudaEventDisableTiming));
+        VS_CUDA(cudaEventRecord(g_partial_ev, s));
+        g_partial_last = s;
     }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
