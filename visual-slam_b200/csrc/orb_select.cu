@@ -329,9 +329,23 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
     const uint8_t* fp = pyr + (size_t)b * plan.pyr_frame_bytes;
     uint8_t* wb = s_blur[wid];
     uint8_t* wr = s_raw[wid];
-    const int u = lane - VS_HALF_PATCH;              // lanes 0..30 <-> columns -15..15 of the disc
-    const int vmax = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;   // the disc is symmetric: |v| <= umax[|u|]
 
+    // disc mask of this lane's patch row (pass A): byte k of word j <-> u = 4j + k - 15
+    uint32_t ic_mask[8];
+    {
+        const int v = lane - VS_HALF_PATCH;
+        const int hw = lane < IC_WIN ? c_umax[v < 0 ? -v : v] : -1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            uint32_t mk = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int uu = 4 * j + k - VS_HALF_PATCH;
+                if ((uu < 0 ? -uu : uu) <= hw) mk |= 255u << (8 * k);
+            }
+            ic_mask[j] = mk;
+        }
+    }
     // Pass A: intensity-centroid angle of this warp's keypoints, one after the other (lane k keeps keypoint
     // k's angle, centre and level).  Then sin/cos in double for all of them at once -- lane k evaluates
     // keypoint k, so the warp pays for one evaluation instead of one per keypoint.  Pass B: steered rBRIEF.
@@ -354,24 +368,30 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
         // ---- intensity-centroid angle (K6) on the unblurred level
         const int x0 = c.x, y0 = c.y;
         const int rxs = (x0 - VS_HALF_PATCH) & ~3;
+        int m10 = 0, m01 = 0;
         __syncwarp();
         if (raw_aligned) stage_window<IC_WIN, IC_WIN_S / 4, true>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane);
         else stage_window<IC_WIN, IC_WIN_S / 4, false>(wr, raw, rpitch, rxs, y0 - VS_HALF_PATCH, lane);
         __syncwarp();
-        int m10 = 0, m01 = 0;
-        {
-            const uint8_t* cc = wr + VS_HALF_PATCH * IC_WIN_S + (x0 - rxs) + u;   // centre row, this lane's column
-            int col = vmax >= 0 ? cc[0] : 0, vs = 0;
+        // lane = patch row: the row's nine staged words (row stride 9 words: conflict-free), funnel-shifted to the
+        // patch's first column, masked to the disc and reduced with two dot products per word (sum of u*I, sum of I)
+        if (lane < IC_WIN) {
+            const uint32_t* p = (const uint32_t*)(wr + lane * IC_WIN_S);
+            uint32_t w[9];
 #pragma unroll
-            for (int v = 1; v <= VS_HALF_PATCH; ++v) {
-                if (v <= vmax) {
-                    const int lo = cc[-v * IC_WIN_S], hi = cc[v * IC_WIN_S];
-                    col += lo + hi;
-                    vs += v * (hi - lo);
-                }
+            for (int j = 0; j < 9; ++j) w[j] = p[j];
+            const int sh = ((x0 - VS_HALF_PATCH) & 3) * 8;
+            int rs = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t q = __funnelshift_r(w[j], w[j + 1], sh) & ic_mask[j];
+                // bytes of word j <-> u = 4j-15 .. 4j-12
+                const uint32_t wu = (uint32_t)((4 * j - 15) & 255) | ((uint32_t)((4 * j - 14) & 255) << 8) |
+                                    ((uint32_t)((4 * j - 13) & 255) << 16) | ((uint32_t)((4 * j - 12) & 255) << 24);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(q), "r"(wu));
+                rs = (int)__dp4a(q, 0x01010101u, (uint32_t)rs);
             }
-            m10 = u * col;
-            m01 = vs;
+            m01 = (lane - VS_HALF_PATCH) * rs;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
