@@ -281,14 +281,26 @@ __device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, i
     const uint8_t* src = img + (size_t)(ys + r0) * pitch + xs + 4 * cw;
     uint32_t* dst = (uint32_t*)win + r0 * WORDS + cw;
     const size_t step = (size_t)pitch * RG;
+    if (ALIGNED) {
+        // aligned rows: asynchronous 4-byte copies global -> shared (LDGSTS), one instruction per word instead of a
+        // load and a store; the caller's __syncwarp follows the wait
+        uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+#pragma unroll
+        for (int k = 0; k < (ROWS + RG - 1) / RG; ++k) {
+            if (k * RG + r0 < ROWS)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+            src += step;
+            d += RG * WORDS * 4;
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        return;
+    }
     uint32_t v[(ROWS + RG - 1) / RG];
 #pragma unroll
     for (int k = 0; k < (ROWS + RG - 1) / RG; ++k) {            // all loads first, then the stores
         v[k] = 0;
-        if (k * RG + r0 < ROWS) {
-            if (ALIGNED) v[k] = __ldg((const uint32_t*)src);
-            else v[k] = (uint32_t)__ldg(src) | ((uint32_t)__ldg(src + 1) << 8) | ((uint32_t)__ldg(src + 2) << 16) | ((uint32_t)__ldg(src + 3) << 24);
-        }
+        if (k * RG + r0 < ROWS)
+            v[k] = (uint32_t)__ldg(src) | ((uint32_t)__ldg(src + 1) << 8) | ((uint32_t)__ldg(src + 2) << 16) | ((uint32_t)__ldg(src + 3) << 24);
         src += step;
     }
 #pragma unroll
