@@ -109,6 +109,17 @@ int vslam_orb_detect_and_compute_host(vslam_orb* orb, const uint8_t* h_frames, i
 int vslam_orb_detect_and_compute_host_bgr(vslam_orb* orb, const uint8_t* h_bgr, int batch,
                                           vslam_keypoint* h_kp, uint8_t* h_desc,
                                           int32_t* h_count);
+/* Replaces cv2.undistort(image, camera_matrix, distortion) (utils.undistort_image,
+ * utils.py:40-52; called between gray conversion and the extractor by tests/test_matcher.py:71,
+ * test_orb_extractor.py:77, run_video.py:149).  uint8 images with 1 or 3 interleaved channels,
+ * [batch][height][pitch]; h_K double [9] row-major, h_dist double [n_dist] with n_dist in
+ * {0, 4, 5, 8, 12} (k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4), both on the host.  Bit-exact with
+ * OpenCV's fixed-point remap (5 fractional map bits, 15-bit bilinear weights, constant border). */
+int vslam_undistort(const uint8_t* d_src, int batch, int height, int width, int channels,
+                    int pitch_src, const double* h_K, const double* h_dist, int n_dist,
+                    uint8_t* d_dst, int pitch_dst, void* stream);
+int vslam_undistort_host(const uint8_t* h_src, int height, int width, int channels,
+                         const double* h_K, const double* h_dist, int n_dist, uint8_t* h_dst);
 /* cv2.cvtColor(COLOR_BGR2GRAY) on device buffers (d_bgr uint8 [n_pixels][3] -> d_gray uint8
  * [n_pixels]); bit-exact with OpenCV's fixed-point formula. */
 int vslam_bgr2gray(const uint8_t* d_bgr, size_t n_pixels, uint8_t* d_gray, void* stream);

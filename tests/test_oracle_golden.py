@@ -149,3 +149,17 @@ def test_orbslam2_oracle_invariants():
     ss = np.array([25, 9, 9, 8], np.int32)
     keep = OS.cell_filter(xs, ys, ss, 640, 480, 20)
     assert keep.tolist() == [True, False, True, True]
+
+
+def test_undistort_oracle_equals_cv2_golden():
+    """oracle/undistort_oracle.py against cv2.undistort outputs produced through the reference's own
+    utils.undistort_image (tests/golden/make_undistort_golden.py): gray and BGR, 0/4/5/8/12 coefficients, a row
+    wider than OpenCV's 4096-px stripe rule."""
+    from oracle import undistort_oracle as U
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "undistort.npz"))
+    for n in range(int(g["n"])):
+        out = U.undistort(g["img%d" % n], g["K%d" % n], g["dist%d" % n])
+        assert np.array_equal(out, g["out%d" % n]), n
+    # zero distortion is the identity (what every shipped config of the reference uses)
+    img = g["img0"]
+    assert np.array_equal(U.undistort(img, g["K0"], np.zeros(5)), img)

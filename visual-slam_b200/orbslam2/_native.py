@@ -47,6 +47,8 @@ def lib():
         L.vslam_orb_detect_and_compute_host.argtypes = [vp, vp, i32, vp, vp, vp]
         L.vslam_orb_detect_and_compute_host_bgr.argtypes = [vp, vp, i32, vp, vp, vp]
         L.vslam_bgr2gray.argtypes = [vp, C.c_size_t, vp, vp]
+        L.vslam_undistort.argtypes = [vp, i32, i32, i32, i32, i32, vp, vp, i32, vp, i32, vp]
+        L.vslam_undistort_host.argtypes = [vp, i32, i32, i32, vp, vp, i32, vp]
         L.vslam_orb_last_status.argtypes = [vp]
         L.vslam_orb_debug_level.argtypes = [vp, i32, i32, i32, vp]
         L.vslam_orb_debug_candidates.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp]

@@ -60,6 +60,25 @@ def score_essential(E, points1, points2, camera_matrix, threshold=1.0):
     return mask
 
 
+def undistort_image(image, camera_matrix, distortion):
+    """utils.py:40-52 `cv2.undistort(image, camera_matrix, distortion)` on the device: uint8 gray or BGR image
+    -> undistorted image of the same shape (bit-exact with OpenCV's fixed-point remap)."""
+    image = np.asarray(image)
+    if image.dtype != np.uint8 or image.ndim not in (2, 3) or (image.ndim == 3 and image.shape[2] not in (1, 3)):
+        raise ValueError("undistort_image: uint8 image with 1 or 3 channels expected")
+    src = np.ascontiguousarray(image)
+    h, w = src.shape[:2]
+    ch = 1 if src.ndim == 2 else src.shape[2]
+    K = np.ascontiguousarray(camera_matrix, np.float64).reshape(3, 3)
+    dist = np.zeros(0) if distortion is None else np.ascontiguousarray(distortion, np.float64).ravel()
+    out = np.empty_like(src)
+    _native.require_gpu()
+    _native.check(_native.lib().vslam_undistort_host(_native.ptr(src), h, w, ch, _native.ptr(K),
+                                                     _native.ptr(dist) if len(dist) else None, len(dist),
+                                                     _native.ptr(out)))
+    return out
+
+
 def triangulate_points(points1, points2, P1, P2):
     """utils.py:56-60 -> float32 [4, N] homogeneous points (as cv2.triangulatePoints returns them)."""
     p1, p2 = _pts(points1), _pts(points2)
