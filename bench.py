@@ -214,13 +214,23 @@ def run_reference_arm(args, rank):
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
                              "sample": "%d frames per step; %s" % (per_step, sample)},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_name(key):
     w, h, nf, _ = WORKLOADS[key]
     return ("%s: synthetic %dx%d gray video, %d ORB feats, %d levels, scale %.1f, FAST thr %d, "
             "BF-Hamming kNN-2 ratio %.2f" % (key.upper(), w, h, nf, N_LEVELS, SCALE, FAST_THR, RATIO))
+
+
+_RESULT_OUT = None
+
+
+def emit(line):
+    """the one JSON line of a run, on the real stdout"""
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -238,8 +248,12 @@ def main():
     ap.add_argument("--track", action="store_true", help="add the batched tracking step (gates + E-RANSAC + recoverPose) to every step")
     ap.add_argument("--ransac", action="store_true", help="add the batched RANSAC-F stage to every step (default for c3)")
     args = ap.parse_args()
-    # stdout carries exactly one JSON line: NCCL's version banner / warnings go to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: file descriptor 1 is pointed at stderr for the whole run (NCCL prints
+    # its version banner to fd 1, torchrun / libraries may chat), and the result goes to the saved descriptor
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":

@@ -342,7 +342,7 @@ def run_gpu_arm(args, rank, world, B):
         if world == 1 and not args.no_cpu:
             fps, cores, kind, sample = BN.cpu_front_end_fps(w, h, nf, [host_frames[k] for k in range(min(B, 64))] * 8)
             line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}
-        print(json.dumps(line), flush=True)
+        BN.emit(line)
     orb.close()
     if world > 1:
         dist.destroy_process_group()
