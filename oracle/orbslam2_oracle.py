@@ -56,7 +56,7 @@ def distribute_octree(rx, ry, score, width, height, n_target):
     corners in quadtree order."""
     if len(rx) == 0 or n_target <= 0:
         return []
-    nini = max(int(np.floor(np.float32(width) / np.float32(height) + np.float32(0.5))), 1)
+    nini = min(max(int(np.floor(np.float32(width) / np.float32(height) + np.float32(0.5))), 1), 255)
     hx = np.float32(width) / np.float32(nini)
     nodes = {}
     for i in range(len(rx)):

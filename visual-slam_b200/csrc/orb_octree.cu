@@ -89,7 +89,7 @@ vs_octree_kernel(const __grid_constant__ VsPlan plan, int ini_thr, int m_lo, int
     const int wcell = (width + ncols - 1) / ncols, hcell = (height + nrows - 1) / nrows;
     const int ncx = (width + wcell - 1) / wcell;                     // cells per row of the bitmap
     int nini = (int)roundf((float)width / (float)height);
-    nini = max(nini, 1);
+    nini = min(max(nini, 1), 255);            // the root index has 8 bits of the key
     const float hx = (float)width / (float)nini;
 
     for (int i = tid; i < 1024; i += OT_THREADS) s_cell[i] = 0;
