@@ -263,6 +263,42 @@ def run_gpu_arm(args, rank, world, B):
         raise RuntimeError("e2e workers disagree on keypoint / match counts")
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
     e2e_fps = world * B * Ke / float(sharding.max_over_ranks(dist, world, t).item())
+    # --track: the clip call (frames in, 4x4 poses out: vslam_track_clip_host) through the same two host threads
+    e2e_track_fps = None
+    if track:
+        pose_out = [(torch.empty((B, 16), dtype=torch.float64).pin_memory(),
+                     torch.empty((B, 4), dtype=torch.int32).pin_memory()) for _ in range(n_workers)]
+
+        def clip_step(k):
+            _native.check(L.vslam_track_clip_host(handles[k].handle, pin_frames.data_ptr(), B, BN.RATIO, _native.ptr(t_K),
+                                                  0.02, 0.999, 1.0, 1000, C.c_uint64(0x5EED),
+                                                  pose_out[k][0].data_ptr(), pose_out[k][1].data_ptr(), None))
+
+        def clip_run(n):
+            errs = []
+
+            def work(k):
+                try:
+                    torch.cuda.set_device(local)
+                    for _ in range(n):
+                        clip_step(k)
+                except Exception as e:
+                    errs.append(e)
+            th = [threading.Thread(target=work, args=(k,)) for k in range(n_workers)]
+            for t_ in th:
+                t_.start()
+            for t_ in th:
+                t_.join()
+            if errs:
+                raise errs[0]
+        clip_run(1)
+        barrier()
+        t0 = time.perf_counter()
+        clip_run(per_worker)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        e2e_track_fps = world * B * Ke / float(sharding.max_over_ranks(dist, world, t).item())
     handles[1].close()
     h2d = B * w * h
     d2h = B * cap * (24 + 32) + B * 4 + (B - 1) * (cap * 12 + 4)
@@ -333,6 +369,9 @@ def run_gpu_arm(args, rank, world, B):
                                               "(non-default option; the `select` slot times the quadtree kernel)")
         if track:
             breakdown["track"] = round(track_ms / K, 4)
+            line["e2e_track"] = {"value": e2e_track_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d,
+                                 "d2h_bytes_per_step": (B - 1) * (12 * 8 + 16),
+                                 "call": "vslam_track_clip_host: frames in, 4x4 relative poses out"}
             st = t_status.cpu().numpy()
             line["config"]["track"] = ("tracker.py:214-254 per pair: displacement gate 0.02, 2 x median distance gate, "
                                        "findEssentialMat(RANSAC, 0.999, 1.0), recoverPose")

@@ -289,6 +289,18 @@ int vslam_track_batched(const vslam_keypoint* d_kp_query, const vslam_keypoint* 
                         int32_t* d_track_count, double* d_E, uint8_t* d_ransac_mask,
                         uint8_t* d_pose_mask, double* d_R, double* d_t, int32_t* d_status,
                         void* stream);
+/* A clip in, a trajectory out: the reference's per-frame loop (Tracker.process_frame,
+ * tracker.py:73-146) for `batch` consecutive gray host frames (2 <= batch <= max_batch):
+ * one upload, extraction, matching and vslam_track_batched on the device, and per frame
+ * pair only the relative pose h_T double [batch-1][16] (row-major 4x4, T = [R t; 0 0 0 1]
+ * as tracker.py:250-253; identity where the pair failed) and h_status int32 [batch-1][4]
+ * (as vslam_track_batched) come back.  h_count int32 [batch] (keypoints per frame) may be
+ * NULL.  The device-side results of the call (keypoints, descriptors, match lists) stay in
+ * the handle's staging buffers. */
+int vslam_track_clip_host(vslam_orb* orb, const uint8_t* h_frames, int batch, double ratio,
+                          const double* h_K, double threshold_percent, double prob, double thr,
+                          int max_iters, uint64_t seed, double* h_T, int32_t* h_status,
+                          int32_t* h_count);
 /* Replaces cv2.triangulatePoints(P1, P2, p1.T, p2.T) (utils.py:59): per-point DLT.
  * h_X float [4][n] (row-major, un-normalised homogeneous, as cv2 returns it). */
 int vslam_triangulate_host(const double* h_P1, const double* h_P2, const float* h_p1,

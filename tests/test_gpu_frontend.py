@@ -247,3 +247,20 @@ def test_track_batched_equals_track_pair_and_reference_gates(synth640):
     assert m == len(ref["query_idx"]) and bool(out["success"][0]) == bool(ref["success"])
     assert np.array_equal(out["track_match"][0, :m, 0], ref["query_idx"])
     h.close()
+
+
+def test_track_clip_host_returns_the_poses_of_track_batched(synth640):
+    """vslam_track_clip_host: frames in, 4x4 relative poses out (tracker.py:250-253), equal to the batched
+    tracking step pair by pair; failed pairs give the identity."""
+    from orbslam2 import frontend
+    from orbslam2._native import OrbHandle
+    frames = synth640.frames(0, 5)
+    h = OrbHandle(640, 480, n_features=2000, max_batch=8)
+    ref = frontend.track_batched(h, frames, K_SYNTH)
+    T, ok, status, count = frontend.track_clip(h, frames, K_SYNTH)
+    assert np.array_equal(count, ref["count"]) and np.array_equal(status, ref["status"]) and ok.all()
+    assert np.array_equal(T, ref["T"])
+    same = np.stack([frames[0], frames[0], frames[1]])
+    T, ok, status, _ = frontend.track_clip(h, same, K_SYNTH)
+    assert not ok[0] and np.array_equal(T[0], np.eye(4)) and ok[1] and np.array_equal(T[1], ref["T"][0])
+    h.close()

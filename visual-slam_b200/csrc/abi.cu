@@ -226,7 +226,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     if (!o) return VSLAM_OK;
     cudaDeviceSynchronize();
     void* ptrs[] = {o->d_pyr, o->d_cand, o->d_stage, o->d_counters, o->d_tab, o->d_status, o->d_knn_idx,
-                    o->d_knn_dist, o->d_frames, o->d_bgr, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
+                    o->d_knn_dist, o->d_frames, o->d_bgr, o->d_track, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
     if (o->stream_in) cudaStreamDestroy(o->stream_in);

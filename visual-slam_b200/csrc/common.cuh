@@ -95,6 +95,7 @@ struct vslam_orb {
     int32_t* d_knn_dist;
     // host staging for *_host entry points
     uint8_t* d_frames;     // [max_batch][h][pitch0]
+    uint8_t* d_track;      // outputs + workspace of vslam_track_clip_host (lazy, one block)
     uint8_t* d_bgr;        // [max_batch][h][w][3] staging of vslam_orb_detect_and_compute_host_bgr (lazy)
     vslam_keypoint* d_kp;
     uint8_t* d_desc;

@@ -236,6 +236,29 @@ def track_batched(handle, frames, camera_matrix, ratio=0.75, threshold_percent=0
     return out
 
 
+def track_clip(handle, frames, camera_matrix, ratio=0.75, threshold_percent=0.02, prob=0.999, threshold=1.0,
+               max_iters=1000, seed=None):
+    """Tracker.process_frame's loop (tracker.py:73-146) over a clip, one library call: `frames` uint8 [B, H, W]
+    go up once, and only the relative poses come back -> (T float64 [B-1, 4, 4], success bool [B-1],
+    status int32 [B-1, 4], count int32 [B]).  Pair p equals `track_batched` / `track_pair` on frames p, p+1
+    (a pair whose status[3] is non-zero had a displacement decision within 1e-9 of the limit and should be
+    re-run through `track_pair`)."""
+    import ctypes as C
+    from .utils import DEFAULT_SEED
+    _native.require_gpu()
+    frames = np.ascontiguousarray(frames, np.uint8)
+    B = frames.shape[0]
+    K = np.ascontiguousarray(camera_matrix, np.float64).reshape(3, 3)
+    T = np.zeros((B - 1, 4, 4), np.float64)
+    status = np.zeros((B - 1, 4), np.int32)
+    count = np.zeros(B, np.int32)
+    _native.check(_native.lib().vslam_track_clip_host(handle.handle, _native.ptr(frames), B, float(ratio), _native.ptr(K),
+                                                      float(threshold_percent), float(prob), float(threshold),
+                                                      int(max_iters), C.c_uint64(DEFAULT_SEED if seed is None else seed),
+                                                      _native.ptr(T), _native.ptr(status), _native.ptr(count)))
+    return T, status[:, 0] == 1, status, count
+
+
 # --------------------------------------------------------------------------- N2: LocalMapper's matcher
 class BFMatcher:
     """Stand-in for `cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)` (local_mapper.py:116): `knnMatch`
