@@ -305,6 +305,28 @@ int vslam_track_clip_host(vslam_orb* orb, const uint8_t* h_frames, int batch, do
  * h_X float [4][n] (row-major, un-normalised homogeneous, as cv2 returns it). */
 int vslam_triangulate_host(const double* h_P1, const double* h_P2, const float* h_p1,
                            const float* h_p2, int n, float* h_X);
+/* Replaces the per-point loop of LocalMapper._cull_map_points (local_mapper.py:205-237): a map
+ * point is kept when it has at least min_observations observations and, walking them in stored
+ * order, none has a reprojection error above max_error (5.0 in the reference):
+ *   P = K [R | t] of the observing keyframe (utils.compute_projection_matrix, utils.py:137-159),
+ *   proj = P [X 1];  err = |proj_xy / proj_z - kp.pt| in float64;  `err > 5.0` rejects (NaN does not).
+ * The map as flat arrays: points double [n_points][3]; observation lists in CSR form --
+ * obs_offset int32 [n_points + 1], obs_keyframe int32 [m] (index into P), obs_xy float [m][2]
+ * (cv2.KeyPoint.pt of the observed keypoint); P double [n_keyframes][12] row-major 3x4.
+ * valid uint8 [n_points]: 1 kept, 0 dropped, VSLAM_CULL_BAD_KEYFRAME for an observation whose
+ * keyframe index is outside [0, n_keyframes) (the host call returns VSLAM_E_INVALID then, where
+ * the reference raises IndexError).  err double [n_points] (may be NULL): the largest error
+ * among the observations the reference looks at (it stops at the first one above the gate). */
+#define VSLAM_CULL_BAD_KEYFRAME 255
+int vslam_cull_map_points(const double* d_points, const int32_t* d_obs_offset,
+                          const int32_t* d_obs_keyframe, const float* d_obs_xy, const double* d_P,
+                          int n_points, int n_keyframes, int min_observations, double max_error,
+                          uint8_t* d_valid, double* d_err, void* stream);
+int vslam_cull_map_points_host(const double* h_points, const int32_t* h_obs_offset,
+                               const int32_t* h_obs_keyframe, const float* h_obs_xy,
+                               const double* h_P, int n_points, int n_keyframes,
+                               int min_observations, double max_error, uint8_t* h_valid,
+                               double* h_err);
 
 #ifdef __cplusplus
 }

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import ROOT, load_golden
+from conftest import GOLDEN, ROOT, load_golden
 
 K_GERARD = np.array([796.7, 0.0, 239.0, 0.0, 787.8, 425.0, 0.0, 0.0, 1.0]).reshape(3, 3)
 K_SYNTH = np.array([[320.0, 0, 320], [0, 320, 240], [0, 0, 1]])
@@ -163,3 +163,18 @@ def test_undistort_oracle_equals_cv2_golden():
     # zero distortion is the identity (what every shipped config of the reference uses)
     img = g["img0"]
     assert np.array_equal(U.undistort(img, g["K0"], np.zeros(5)), img)
+
+
+def test_cull_oracle_equals_reference_local_mapper():
+    """oracle/cull_oracle.py keeps exactly the map points the reference's LocalMapper._cull_map_points kept
+    (tests/golden/cull.npz, generated by make_cull_golden.py from local_mapper.py:205-245)."""
+    from oracle import cull_oracle
+    g = np.load(os.path.join(GOLDEN, "cull.npz"))
+    for c in range(int(g["n"])):
+        p = "c%d_" % c
+        P = cull_oracle.projection_matrices(g[p + "K"], g[p + "poses"])
+        kp_off, kp_xy = g[p + "kp_off"], g[p + "kp_xy"]
+        obs_xy = kp_xy[kp_off[g[p + "obs_kf"]] + g[p + "obs_kp"]] if len(g[p + "obs_kf"]) else np.zeros((0, 2), np.float32)
+        valid, err = cull_oracle.cull(g[p + "points"], g[p + "offs"], g[p + "obs_kf"], obs_xy, P, int(g[p + "min_obs"]))
+        assert np.array_equal(np.flatnonzero(valid).astype(np.int32), g[p + "kept"]), c
+        assert np.all(err[valid] <= 5.0)

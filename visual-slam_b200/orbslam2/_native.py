@@ -64,6 +64,8 @@ def lib():
         L.vslam_track_batched.argtypes = [vp, vp, i32, vp, vp, i32, i32, vp, i32, i32, f64, f64, f64, i32, C.c_uint64,
                                           vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.vslam_track_clip_host.argtypes = [vp, vp, i32, f64, vp, f64, f64, f64, i32, C.c_uint64, vp, vp, vp]
+        L.vslam_cull_map_points.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, f64, vp, vp, vp]
+        L.vslam_cull_map_points_host.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, f64, vp, vp]
         L.vslam_frontend_run.argtypes = [vp, vp, i32, i32, vp, vp, f64, vp, vp, vp, vp, vp, vp]
         L.vslam_frontend_run_host.argtypes = [vp, vp, i32, f64, vp, vp, vp, vp, vp]
         L.vslam_orb_set_profiling.argtypes = [vp, i32]

@@ -325,10 +325,71 @@ class _Cv2Proxy:
 
 def install_local_mapper_adaptor(module):
     """Point `module.cv2` (e.g. the reference's `orbslam2.local_mapper`) at the proxy above, so that its
-    private matcher and fundamental-matrix RANSAC use the B200 kernels.  Returns the proxy; undo with
-    `module.cv2 = proxy._cv2`."""
+    private matcher and fundamental-matrix RANSAC use the B200 kernels, and -- when the module defines
+    `LocalMapper` -- replace `LocalMapper._cull_map_points` by the device version.  Returns the proxy; undo
+    with `module.cv2 = proxy._cv2` (and `module.LocalMapper._cull_map_points = proxy._cull`)."""
     import cv2
     _native.require_gpu()
     proxy = _Cv2Proxy(cv2)
     module.cv2 = proxy
+    cls = getattr(module, "LocalMapper", None)
+    if cls is not None and hasattr(cls, "_cull_map_points"):
+        proxy._cull = cls._cull_map_points
+        cls._cull_map_points = _cull_map_points_method
     return proxy
+
+
+# --------------------------------------------------------------------------- N2: LocalMapper's map-point culling
+def reprojection_cull(points, obs_offset, obs_keyframe, obs_xy, projections, min_observations=2, max_error=5.0):
+    """The per-point test of LocalMapper._cull_map_points (local_mapper.py:205-237) on flat arrays, on the GPU:
+    points [n, 3]; CSR observation lists obs_offset [n + 1], obs_keyframe [m], obs_xy [m, 2] (kp.pt);
+    projections [n_kf, 3, 4] = K [R | t] per keyframe.  -> (valid bool [n], err float64 [n])."""
+    _native.require_gpu()
+    pts = np.ascontiguousarray(np.asarray(points, np.float64).reshape(-1, 3))
+    off = np.ascontiguousarray(obs_offset, np.int32)
+    kf = np.ascontiguousarray(obs_keyframe, np.int32)
+    xy = np.ascontiguousarray(np.asarray(obs_xy, np.float32).reshape(-1, 2))
+    P = np.ascontiguousarray(np.asarray(projections, np.float64).reshape(-1, 12))
+    n = len(pts)
+    if len(off) != n + 1 or len(kf) != len(xy) or (n and int(off[-1]) != len(kf)):
+        raise ValueError("observation lists do not match the points")
+    valid, err = np.zeros(n, np.uint8), np.zeros(n, np.float64)
+    _native.check(_native.lib().vslam_cull_map_points_host(_native.ptr(pts), _native.ptr(off), _native.ptr(kf),
+                                                           _native.ptr(xy), _native.ptr(P), n, len(P),
+                                                           int(min_observations), float(max_error),
+                                                           _native.ptr(valid), _native.ptr(err)))
+    return valid == 1, err
+
+
+def cull_map_points(map_points, keyframes, camera_matrix, min_observations=2, max_error=5.0):
+    """LocalMapper._cull_map_points' first half on the reference's own structures: `map_points` is the list of
+    dicts with 'position' and 'observed_keyframes' {keyframe index: keypoint index}, `keyframes` the list of
+    dicts with 'keypoints' (cv2.KeyPoint) and 'pose' (4x4).  Returns the surviving dicts, in order."""
+    from .utils import compute_projection_matrix
+    if not map_points:
+        return []
+    P = np.zeros((len(keyframes), 3, 4))
+    for k, kf in enumerate(keyframes):
+        P[k] = compute_projection_matrix(kf['pose'][:3, :3], kf['pose'][:3, 3], camera_matrix)
+    off, okf, oxy = [0], [], []
+    for mp in map_points:
+        for kf_id, kp_id in mp.get('observed_keyframes', {}).items():
+            okf.append(kf_id)
+            oxy.append(keyframes[kf_id]['keypoints'][kp_id].pt)      # IndexError like the reference's lookup
+        off.append(len(okf))
+    pos = np.array([np.asarray(mp['position'], np.float64).reshape(3) for mp in map_points])
+    valid, _ = reprojection_cull(pos, off, okf, np.asarray(oxy, np.float32).reshape(-1, 2), P, min_observations, max_error)
+    return [mp for mp, v in zip(map_points, valid) if v]
+
+
+def _cull_map_points_method(self):
+    """Drop-in body for LocalMapper._cull_map_points (local_mapper.py:205-245): the per-point test on the GPU,
+    then the per-keyframe id lists rebuilt like local_mapper.py:240-245 (same order, one pass)."""
+    self.map_points = cull_map_points(self.map_points, self.keyframes, self.camera_matrix, self.min_observations)
+    lists = {kf['id']: [] for kf in self.keyframes}
+    for mp in self.map_points:
+        for kf_id in mp.get('observed_keyframes', {}):
+            if kf_id in lists:
+                lists[kf_id].append(mp['id'])
+    for kf in self.keyframes:
+        kf['map_points'] = lists[kf['id']]
