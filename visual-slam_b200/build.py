@@ -14,7 +14,7 @@ OUT = os.path.join(HERE, "orbslam2", "libvslam_b200.so")
 BUILD = os.path.join(HERE, "build")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-fmad=false"]
+         "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-fmad=false"] + os.environ.get("VSLAM_NVCC_FLAGS", "").split()
 
 
 def sources():

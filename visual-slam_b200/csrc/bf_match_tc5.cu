@@ -14,17 +14,21 @@
 //     expansion writes that layout directly (the k order of a dot product is free, so k = bit index),
 //   * a train set is expanded ONCE (vs_knn2_expand_kernel: operand tile + 16-bit key constants, 33 024 B
 //     per 128 descriptors, L2 resident for the CTAs of the same pair) instead of by every CTA that reads it,
-//   * a producer warp streams those tiles into a 3-stage shared-memory ring with bulk async copies (TMA,
-//     mbarrier complete_tx), issues 2 x 8 tcgen05.mma (M128 N128 K32, u8 x u8 -> s32) per tile into one of
-//     two 256-column TMEM buffers and commits to an mbarrier,
-//   * 16 consumer warps read finished tiles back with tcgen05.ld 32x32b (thread = TMEM lane = query row, so
-//     the top-2 state is private to a thread) and release the TMEM buffer / ring stage through an mbarrier;
-//     there is no CTA-wide barrier in the tile loop.
+//   * a loader warp streams those tiles into a 3-stage shared-memory ring with bulk async copies (TMA,
+//     mbarrier complete_tx),
+//   * two MMA warps take turns (even / odd tiles = TMEM buffer 0 / 1): 2 x 8 tcgen05.mma (M128 N128 K32,
+//     u8 x u8 -> s32) per tile into a 256-column TMEM buffer, then tcgen05.commit to an mbarrier.  The warp walks
+//     its loop with warp-uniform values so that the descriptors are built on the uniform datapath (1-3
+//     instructions between MMAs; a lane-0 branch costs ~16 with a waterfall loop per MMA and made the issue
+//     thread, not the tensor pipe, the bottleneck -- tools/knn_trace.py shows the timeline),
+//   * 16 consumer warps read finished tiles back with tcgen05.ld 32x32b.pack::16b (thread = TMEM lane = query
+//     row, so the top-2 state is private to a thread; two dot products per register) and release the TMEM
+//     buffer / ring stage through mbarriers; there is no CTA-wide barrier in the tile loop.
 #include "common.cuh"
 
 #define T5_ROWS 256          // query rows per CTA
 #define T5_CONSUMERS 512     // 16 warps: warps w and w + 8 read the same TMEM lanes, one column half each
-#define T5_THREADS 544       // + the producer warp
+#define T5_THREADS 608       // + MMA warp 0 (16), the loader warp (17), MMA warp 1 (18)
 #define T5_STAGES 3
 #define T5_N 128             // train descriptors per tile
 #define T5_OPER_BYTES 32768  // one 128-row operand tile: 16 groups x 2048 B
@@ -88,30 +92,32 @@ __device__ __forceinline__ void t5_top2_u16x2(uint32_t& k1, uint32_t& k2, uint32
     k2 = n2;
 }
 
-// 32 consecutive accumulator columns of this thread's TMEM lane (asynchronous until tcgen05.wait::ld)
-__device__ __forceinline__ void t5_tmem_ld32(uint32_t (&v)[32], uint32_t taddr)
+// 32 consecutive accumulator columns of this thread's TMEM lane as 16 registers: .pack::16b keeps the low 16 bits
+// of each column (a dot product is <= 256) and packs columns 2j / 2j+1 into the low / high half of register j --
+// already the 16x2 lane form of the keys, at half the TMEM read time of a plain load (tools/ubench/ldtm.cu; TMEM
+// reads and the MMAs' accumulator traffic share the TMEM port, so read time is MMA time).  Asynchronous until
+// tcgen05.wait::ld.
+__device__ __forceinline__ void t5_tmem_ld32p(uint32_t (&v)[16], uint32_t taddr)
 {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr));
 }
 
-// fold 32 dot products into the packed top-2 pair: c2[j] holds the 16-bit key constants of columns 2j (low
-// lane) and 2j+1 (high lane); key = constant - 128 dot never borrows (it is >= 0 per lane)
-__device__ __forceinline__ void t5_reduce32(const uint32_t (&v)[32], const uint32_t* c2, uint32_t& p1, uint32_t& p2)
+// fold 32 dot products (16 packed registers) into the packed top-2 pair: c2[j] holds the 16-bit key constants of
+// columns 2j (low lane) and 2j+1 (high lane); key = constant - 128 dot never borrows (it is >= 0 per lane), so one
+// 32-bit multiply-add forms both lanes
+__device__ __forceinline__ void t5_reduce32(const uint32_t (&v)[16], const uint32_t* c2, uint32_t& p1, uint32_t& p2)
 {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
         const uint4 cc = *(const uint4*)(c2 + j);
-        const uint32_t a = v[2 * j + 1] * 0xff800000u + (v[2 * j] * 0xffffff80u + cc.x);
-        const uint32_t b = v[2 * j + 3] * 0xff800000u + (v[2 * j + 2] * 0xffffff80u + cc.y);
-        const uint32_t c = v[2 * j + 5] * 0xff800000u + (v[2 * j + 4] * 0xffffff80u + cc.z);
-        const uint32_t d = v[2 * j + 7] * 0xff800000u + (v[2 * j + 6] * 0xffffff80u + cc.w);
+        const uint32_t a = v[j] * 0xffffff80u + cc.x;
+        const uint32_t b = v[j + 1] * 0xffffff80u + cc.y;
+        const uint32_t c = v[j + 2] * 0xffffff80u + cc.z;
+        const uint32_t d = v[j + 3] * 0xffffff80u + cc.w;
         t5_top2_u16x2(p1, p2, a, b);
         t5_top2_u16x2(p1, p2, c, d);
     }
@@ -128,6 +134,17 @@ __device__ __forceinline__ void t5_wait(uint32_t bar, uint32_t parity)
         " @p bra D%=;\n bra W%=;\n"
         "D%=:\n}\n" ::"r"(bar), "r"(parity) : "memory");
 }
+
+#ifdef T5_TRACE
+// timeline of CTA (0, 0, 0), clock64 per tile i: [0] MMAs issued + commit, [1] consumer warp 0 sees the
+// accumulators, [2] consumer warp 0 done, [3] loader issued the tile, [4] MMA warp saw the free TMEM buffer,
+// [5] MMA warp about to issue, [6] last consumer warp done (tools/knn_trace.py; build with -DT5_TRACE)
+__device__ long long t5_trace_buf[8 * 64];
+extern "C" int vslam_debug_t5_trace(long long* out) { return (int)cudaMemcpyFromSymbol(out, t5_trace_buf, sizeof(t5_trace_buf)); }
+#define T5_STAMP(row, i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) < 64) t5_trace_buf[(row) * 64 + (i)] = clock64(); } while (0)
+#else
+#define T5_STAMP(row, i) do { } while (0)
+#endif
 
 // ---- train descriptors -> UMMA operand tiles + key constants (once per train set) ------------------
 // thread = (train row, quarter) with consecutive lanes on consecutive rows; quarter 0 also counts the row's bits
@@ -162,9 +179,9 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
                    int32_t* __restrict__ out_dist)
 {
     extern __shared__ __align__(128) uint8_t t5_smem[];
-    // full[s]: tile landed in ring stage s; done[b]: MMAs into TMEM buffer b finished; free[b]: all 16 consumer
-    // warps are through with TMEM buffer b (and with the ring stage of that tile)
-    __shared__ __align__(8) unsigned long long s_full[T5_STAGES], s_done[2], s_free[2];
+    // full[s]: tile landed in ring stage s; empty[s]: all 16 consumer warps are through with the tile in stage s;
+    // done[b]: MMAs into TMEM buffer b finished; free[b]: all 16 consumer warps are through with TMEM buffer b
+    __shared__ __align__(8) unsigned long long s_full[T5_STAGES], s_empty[T5_STAGES], s_done[2], s_free[2], s_turn[2];
     __shared__ uint32_t s_tmem;
     __shared__ int2 s_merge[T5_ROWS];
     const int pair = blockIdx.z, split = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -190,6 +207,8 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     const uint32_t full_u = (uint32_t)__cvta_generic_to_shared(&s_full[0]);
     const uint32_t done_u = (uint32_t)__cvta_generic_to_shared(&s_done[0]);
     const uint32_t free_u = (uint32_t)__cvta_generic_to_shared(&s_free[0]);
+    const uint32_t empty_u = (uint32_t)__cvta_generic_to_shared(&s_empty[0]);
+    const uint32_t turn_u = (uint32_t)__cvta_generic_to_shared(&s_turn[0]);
 
     // ---- TMEM (all 512 columns: two buffers of 2 x 128), barriers
     if (wid == 0) {
@@ -197,9 +216,13 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (tid == 0) {
-        for (int k = 0; k < T5_STAGES; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_u + 8 * k));
+        for (int k = 0; k < T5_STAGES; ++k) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_u + 8 * k));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty_u + 8 * k), "r"(T5_CONSUMERS / 32));
+        }
         for (int k = 0; k < 2; ++k) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(done_u + 8 * k));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(turn_u + 8 * k));
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(free_u + 8 * k), "r"(T5_CONSUMERS / 32));
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -226,42 +249,65 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
     const uint32_t tmem = s_tmem;
 
     int k1 = 0x7fffffff, k2 = 0x7fffffff;       // running pair of widened keys
-    if (!consumer) {
-        // ---- producer: ring loads, MMA issue (one thread)
+    if (wid == T5_CONSUMERS / 32 + 1) {
+        // ---- loader (one thread): train tiles into the ring; stage s is reusable once all 16 consumer warps are
+        // through with the tile that was in it (which also means its MMAs are complete)
         if (lane == 0) {
             const uint8_t* src = expanded + ((size_t)pair * tiles_max + t_begin) * T5_TILE_BYTES;
-            auto load = [&](int i) {
-                const uint32_t bar = full_u + 8 * (i % T5_STAGES), dst = sT_u + (i % T5_STAGES) * T5_TILE_BYTES;
+            for (int i = 0; i < ntile; ++i) {
+                const int stage = i % T5_STAGES;
+                if (i >= T5_STAGES) t5_wait(empty_u + 8 * stage, (uint32_t)(i / T5_STAGES - 1) & 1u);
+                const uint32_t bar = full_u + 8 * stage, dst = sT_u + stage * T5_TILE_BYTES;
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(T5_TILE_BYTES) : "memory");
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                              ::"r"(dst), "l"(src + (size_t)i * T5_TILE_BYTES), "r"(T5_TILE_BYTES), "r"(bar) : "memory");
-            };
-            for (int i = 0; i < T5_STAGES && i < ntile; ++i) load(i);
+                T5_STAMP(3, i);
+            }
+        }
+    } else if (!consumer) {
+        // ---- MMA issue: one thread in each of two warps, even / odd tiles (= TMEM buffer 0 / 1).  The tensor pipe
+        // takes a few MMAs ahead and then blocks the issuing thread, so a single issuer reaches the barrier waits of
+        // the next tile only when the pipe is already draining; with two, the other thread has those waits behind
+        // it and only needs its turn (tiles must enter the pipe in order: the consumers want tile i first).
+        // The whole warp walks the loop with warp-uniform values (REDUX results, constants), so the descriptors are
+        // formed on the uniform datapath; one elected lane issues.
+        {
+            const int me = (int)__reduce_min_sync(0xffffffffu, (unsigned)(wid == T5_CONSUMERS / 32 ? 0 : 1));
+            const int ntile_u = (int)__reduce_min_sync(0xffffffffu, (unsigned)ntile);
+            const uint32_t tmem_u = __reduce_min_sync(0xffffffffu, tmem);
             const uint32_t idesc = (2u << 4) | ((uint32_t)(T5_N >> 3) << 17) | ((128u >> 4) << 24);   // s32 accum, u8 x u8, K-major both
-            for (int i = 0; i < ntile; ++i) {
-                const int buf = i & 1;
-                if (i >= 2) {
-                    // epilogue of tile i - 2 is over: its TMEM buffer (this tile's) and its ring stage are free
+            uint32_t elected;
+            asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(elected));
+            for (int i = me; i < ntile_u; i += 2) {
+                const int buf = me, stage = i % T5_STAGES;
+                if (i >= 2) {      // epilogue of tile i - 2 is over: its TMEM buffer is this tile's
                     t5_wait(free_u + 8 * buf, (uint32_t)((i - 2) >> 1) & 1u);
-                    if (i + 1 < ntile && i + 1 >= T5_STAGES) load(i + 1);          // stage (i + 1) % 3 == (i - 2) % 3
+                    T5_STAMP(4, i);
                 }
-                t5_wait(full_u + 8 * (i % T5_STAGES), (uint32_t)(i / T5_STAGES) & 1u);
+                t5_wait(full_u + 8 * stage, (uint32_t)(i / T5_STAGES) & 1u);
+                if (i >= 1) t5_wait(turn_u + 8 * me, (uint32_t)(((i + 1) >> 1) - 1) & 1u);   // tile i - 1 is in the pipe
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
-                for (int m = 0; m < 2; ++m) {
-                    const uint32_t tacc = tmem + buf * 256 + m * 128;
+                T5_STAMP(5, i);
+                if (elected) {
 #pragma unroll
                     for (int s = 0; s < 8; ++s) {
-                        const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
-                        const uint64_t db = t5_smem_desc(sT_u + (i % T5_STAGES) * T5_TILE_BYTES + s * 256);
-                        const uint32_t accumulate = s > 0;
-                        asm volatile(
-                            "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
-                            " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
-                            ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+#pragma unroll
+                        for (int m = 0; m < 2; ++m) {          // the two M-tiles alternate: independent accumulators back to back
+                            const uint32_t tacc = tmem_u + buf * 256 + m * 128;
+                            const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
+                            const uint64_t db = t5_smem_desc(sT_u + stage * T5_TILE_BYTES + s * 256);
+                            const uint32_t accumulate = s > 0;
+                            asm volatile(
+                                "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                                " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
+                                ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+                        }
                     }
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(done_u + 8 * buf) : "memory");
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(turn_u + 8 * (me ^ 1)) : "memory");
                 }
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(done_u + 8 * buf) : "memory");
+                __syncwarp();
+                T5_STAMP(0, i);
             }
         }
     } else {
@@ -271,24 +317,33 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
             t5_wait(full_u + 8 * stage, (uint32_t)(i / T5_STAGES) & 1u);     // the tile's key constants (acquire)
             t5_wait(done_u + 8 * buf, (uint32_t)(i >> 1) & 1u);              // its accumulators
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (tid == 0) T5_STAMP(1, i);
             const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + mtile * 128 + chalf * 64;
             const uint32_t* cbase = (const uint32_t*)(sT + stage * T5_TILE_BYTES + T5_OPER_BYTES) + chalf * 32;
             // this warp's 64 columns as two 32-column chunks, the second load in flight while the first is reduced
-            uint32_t va[32], vb[32];
+            uint32_t va[16], vb[16];
             uint32_t p1 = 0xffffffffu, p2 = 0xffffffffu;
-            t5_tmem_ld32(va, taddr);
+            t5_tmem_ld32p(va, taddr);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            t5_tmem_ld32(vb, taddr + 32);
+            t5_tmem_ld32p(vb, taddr + 32);
             t5_reduce32(va, cbase, p1, p2);
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             t5_reduce32(vb, cbase + 16, p1, p2);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(free_u + 8 * buf) : "memory");
+            if (lane == 0) {
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(free_u + 8 * buf) : "memory");
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_u + 8 * stage) : "memory");
+            }
+#ifdef T5_TRACE
+            if (lane == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && i < 64)
+                atomicMax((unsigned long long*)&t5_trace_buf[6 * 64 + i], (unsigned long long)clock64());
+#endif
             // the tile's four survivors (two per lane) join the running pair
             const int base = (t_begin + i) * T5_N + chalf * 64;
             t5_top2(k1, k2, t5_widen(p1 & 0xffffu, base), t5_widen(p1 >> 16, base));
             t5_top2(k1, k2, t5_widen(p2 & 0xffffu, base), t5_widen(p2 >> 16, base));
+            if (tid == 0) T5_STAMP(2, i);
         }
     }
     // merge the two column halves (two sorted pairs -> the two smallest of the four keys)
