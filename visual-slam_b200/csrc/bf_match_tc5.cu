@@ -17,7 +17,7 @@
 //   * a loader warp streams those tiles into a 3-stage shared-memory ring with bulk async copies (TMA,
 //     mbarrier complete_tx),
 //   * two MMA warps take turns (even / odd tiles = TMEM buffer 0 / 1): 2 x 8 tcgen05.mma (M128 N128 K32,
-//     u8 x u8 -> s32) per tile into a 256-column TMEM buffer, then tcgen05.commit to an mbarrier.  The warp walks
+//     u8 x u8 -> s32) per tile into a 256-column TMEM buffer, one tcgen05.commit per M-tile.  The warp walks
 //     its loop with warp-uniform values so that the descriptors are built on the uniform datapath (1-3
 //     instructions between MMAs; a lane-0 branch costs ~16 with a waterfall loop per MMA and made the issue
 //     thread, not the tensor pipe, the bottleneck -- tools/knn_trace.py shows the timeline),
@@ -180,8 +180,10 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
 {
     extern __shared__ __align__(128) uint8_t t5_smem[];
     // full[s]: tile landed in ring stage s; empty[s]: all 16 consumer warps are through with the tile in stage s;
-    // done[b]: MMAs into TMEM buffer b finished; free[b]: all 16 consumer warps are through with TMEM buffer b
-    __shared__ __align__(8) unsigned long long s_full[T5_STAGES], s_empty[T5_STAGES], s_done[2], s_free[2], s_turn[2];
+    // done[2b + m]: the MMAs of M-tile m into TMEM buffer b finished; free[2b + m]: the 8 consumer warps of that
+    // M-tile are through with it (hand-off per M-tile: four units in flight instead of two); turn[w]: MMA warp w
+    // may issue (the other warp's tile is in the pipe)
+    __shared__ __align__(8) unsigned long long s_full[T5_STAGES], s_empty[T5_STAGES], s_done[4], s_free[4], s_turn[2];
     __shared__ uint32_t s_tmem;
     __shared__ int2 s_merge[T5_ROWS];
     const int pair = blockIdx.z, split = blockIdx.y, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -215,17 +217,29 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(&s_tmem)));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    if (tid == 0) {
+    const int tiles = (nt + T5_N - 1) / T5_N;
+    const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
+    const int ntile = t_end - t_begin;
+    const uint8_t* tile_src = expanded + ((size_t)pair * tiles_max + t_begin) * T5_TILE_BYTES;
+    auto load_tile = [&](int i) {
+        const uint32_t bar = full_u + 8 * (i % T5_STAGES), dst = sT_u + (i % T5_STAGES) * T5_TILE_BYTES;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(T5_TILE_BYTES) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(tile_src + (size_t)i * T5_TILE_BYTES), "r"(T5_TILE_BYTES), "r"(bar) : "memory");
+    };
+    if (wid == T5_CONSUMERS / 32 + 1 && lane == 0) {      // the loader thread: barriers, then the first ring fill
         for (int k = 0; k < T5_STAGES; ++k) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(full_u + 8 * k));
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty_u + 8 * k), "r"(T5_CONSUMERS / 32));
         }
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < 4; ++k) {      // per (TMEM buffer, M-tile): 8 consumer warps read one M-tile
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(done_u + 8 * k));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(turn_u + 8 * k));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(free_u + 8 * k), "r"(T5_CONSUMERS / 32));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(free_u + 8 * k), "r"(T5_CONSUMERS / 64));
         }
+        for (int k = 0; k < 2; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(turn_u + 8 * k));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // the first tiles land while the other warps expand the query rows
+        for (int i = 0; i < T5_STAGES && i < ntile; ++i) { load_tile(i); T5_STAMP(3, i); }
     }
     // ---- query rows -> A operand, popc(a) of this thread's row
     const uint8_t* qbase = query + (size_t)pair * q_stride * 32;
@@ -238,9 +252,6 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         const uint4 x = __ldg(qp), y = __ldg(qp + 1);
         pa = __popc(x.x) + __popc(x.y) + __popc(x.z) + __popc(x.w) + __popc(y.x) + __popc(y.y) + __popc(y.z) + __popc(y.w);
     }
-    const int tiles = (nt + T5_N - 1) / T5_N;
-    const int t_begin = (int)((long)tiles * split / nsplit), t_end = (int)((long)tiles * (split + 1) / nsplit);
-    const int ntile = t_end - t_begin;
 
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -253,14 +264,9 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         // ---- loader (one thread): train tiles into the ring; stage s is reusable once all 16 consumer warps are
         // through with the tile that was in it (which also means its MMAs are complete)
         if (lane == 0) {
-            const uint8_t* src = expanded + ((size_t)pair * tiles_max + t_begin) * T5_TILE_BYTES;
-            for (int i = 0; i < ntile; ++i) {
-                const int stage = i % T5_STAGES;
-                if (i >= T5_STAGES) t5_wait(empty_u + 8 * stage, (uint32_t)(i / T5_STAGES - 1) & 1u);
-                const uint32_t bar = full_u + 8 * stage, dst = sT_u + stage * T5_TILE_BYTES;
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(T5_TILE_BYTES) : "memory");
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(dst), "l"(src + (size_t)i * T5_TILE_BYTES), "r"(T5_TILE_BYTES), "r"(bar) : "memory");
+            for (int i = T5_STAGES; i < ntile; ++i) {
+                t5_wait(empty_u + 8 * (i % T5_STAGES), (uint32_t)(i / T5_STAGES - 1) & 1u);
+                load_tile(i);
                 T5_STAMP(3, i);
             }
         }
@@ -280,20 +286,18 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
             asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(elected));
             for (int i = me; i < ntile_u; i += 2) {
                 const int buf = me, stage = i % T5_STAGES;
-                if (i >= 2) {      // epilogue of tile i - 2 is over: its TMEM buffer is this tile's
-                    t5_wait(free_u + 8 * buf, (uint32_t)((i - 2) >> 1) & 1u);
-                    T5_STAMP(4, i);
-                }
                 t5_wait(full_u + 8 * stage, (uint32_t)(i / T5_STAGES) & 1u);
                 if (i >= 1) t5_wait(turn_u + 8 * me, (uint32_t)(((i + 1) >> 1) - 1) & 1u);   // tile i - 1 is in the pipe
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                T5_STAMP(5, i);
-                if (elected) {
 #pragma unroll
-                    for (int s = 0; s < 8; ++s) {
+                for (int m = 0; m < 2; ++m) {
+                    // the 8 warps that read M-tile m of tile i - 2 are through with this half of the TMEM buffer
+                    if (i >= 2) t5_wait(free_u + 8 * (2 * buf + m), (uint32_t)((i - 2) >> 1) & 1u);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    if (m == 0) T5_STAMP(5, i);
+                    if (elected) {
+                        const uint32_t tacc = tmem_u + buf * 256 + m * 128;
 #pragma unroll
-                        for (int m = 0; m < 2; ++m) {          // the two M-tiles alternate: independent accumulators back to back
-                            const uint32_t tacc = tmem_u + buf * 256 + m * 128;
+                        for (int s = 0; s < 8; ++s) {
                             const uint64_t da = t5_smem_desc(sA_u + m * T5_OPER_BYTES + s * 256);
                             const uint64_t db = t5_smem_desc(sT_u + stage * T5_TILE_BYTES + s * 256);
                             const uint32_t accumulate = s > 0;
@@ -302,11 +306,12 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
                                 " tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n}\n"
                                 ::"r"(tacc), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
                         }
+                        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                     ::"r"(done_u + 8 * (2 * buf + m)) : "memory");
+                        if (m == 1) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(turn_u + 8 * (me ^ 1)) : "memory");
                     }
-                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(done_u + 8 * buf) : "memory");
-                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(turn_u + 8 * (me ^ 1)) : "memory");
+                    __syncwarp();
                 }
-                __syncwarp();
                 T5_STAMP(0, i);
             }
         }
@@ -315,7 +320,7 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
         for (int i = 0; i < ntile; ++i) {
             const int buf = i & 1, stage = i % T5_STAGES;
             t5_wait(full_u + 8 * stage, (uint32_t)(i / T5_STAGES) & 1u);     // the tile's key constants (acquire)
-            t5_wait(done_u + 8 * buf, (uint32_t)(i >> 1) & 1u);              // its accumulators
+            t5_wait(done_u + 8 * (2 * buf + mtile), (uint32_t)(i >> 1) & 1u);   // its accumulators (this warp's M-tile)
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (tid == 0) T5_STAMP(1, i);
             const uint32_t taddr = tmem + (((uint32_t)(wid & 3) * 32u) << 16) + buf * 256 + mtile * 128 + chalf * 64;
@@ -332,7 +337,7 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) {
-                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(free_u + 8 * buf) : "memory");
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(free_u + 8 * (2 * buf + mtile)) : "memory");
                 asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty_u + 8 * stage) : "memory");
             }
 #ifdef T5_TRACE
