@@ -96,6 +96,7 @@ __device__ __forceinline__ float harris_response(const uint8_t* img, int pitch, 
 }
 
 #define VS_HARRIS_CTAS 4
+#define VS_HARRIS_LIST 1024
 
 __global__ void __launch_bounds__(256)
 vs_harris_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frames, int fpitch,
@@ -129,16 +130,44 @@ vs_harris_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict_
     else { img = pyr + (size_t)b * plan.pyr_frame_bytes + L.raw_off; pitch = L.pitch; }
     VsCand* cl = cand + (size_t)b * plan.cand_frame_entries + L.cand_off;
     const bool aligned = (((size_t)img | (size_t)pitch) & 3) == 0;
+    // Only the candidates at or above the cut get a response (a quarter of them on textured frames), so they are
+    // compacted into a shared list first and the 400-instruction response runs on full warps.
+    __shared__ uint2 s_todo[VS_HARRIS_LIST];      // (index in the candidate list, y << 16 | x)
+    __shared__ int s_ntodo;
+    if (tid == 0) s_ntodo = 0;
+    __syncthreads();
     int nsurv = 0;
-    for (int i = blockIdx.x * 256 + tid; i < ncand; i += VS_HARRIS_CTAS * 256) {
-        VsCand c = cl[i];
-        uint32_t key = 0;
-        if ((int)c.v >= thr) {
-            key = f2key(aligned ? harris_response<true>(img, pitch, c.x, c.y) : harris_response<false>(img, pitch, c.x, c.y));
-            if (key == 0) key = 1;
-            ++nsurv;
+    const int lane = tid & 31;
+    for (int base = blockIdx.x * 256; base < ncand; base += VS_HARRIS_CTAS * 256) {
+        const int i = base + tid;
+        bool sv = false;
+        VsCand c;
+        if (i < ncand) {
+            c = cl[i];
+            sv = (int)c.v >= thr;
+            if (!sv) cl[i].v = 0;
         }
-        cl[i].v = key;
+        const uint32_t m = __ballot_sync(0xffffffffu, sv);
+        int pos = 0;
+        if (lane == 0 && m) pos = atomicAdd(&s_ntodo, __popc(m));
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+        if (sv) s_todo[pos + __popc(m & ((1u << lane) - 1u))] = make_uint2((uint32_t)i, ((uint32_t)c.y << 16) | c.x);
+        __syncthreads();
+        const int n = s_ntodo;
+        const bool last = base + VS_HARRIS_CTAS * 256 >= ncand;
+        if (n > VS_HARRIS_LIST - 256 || last) {       // the next chunk might not fit: drain
+            for (int j = tid; j < n; j += 256) {
+                const uint2 e = s_todo[j];
+                const int x = (int)(e.y & 0xffff), y = (int)(e.y >> 16);
+                uint32_t key = f2key(aligned ? harris_response<true>(img, pitch, x, y) : harris_response<false>(img, pitch, x, y));
+                if (key == 0) key = 1;
+                cl[e.x].v = key;
+                ++nsurv;
+            }
+            __syncthreads();
+            if (tid == 0) s_ntodo = 0;
+            __syncthreads();
+        }
     }
     // survivor count (warp-aggregated)
 #pragma unroll
