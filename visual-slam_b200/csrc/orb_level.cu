@@ -32,7 +32,7 @@
 #define BL_ROWS (VS_TH + 6)
 #define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
 #ifndef VS_LEVEL_CTAS
-#define VS_LEVEL_CTAS 5                // resident CTAs per SM the register budget is capped for (48 registers)
+#define VS_LEVEL_CTAS 6                // resident CTAs per SM the register budget is capped for (40 registers)
 #endif
 
 // getGaussianKernel(7, 2, CV_32F) of cv2 4.13, taps outer..centre (bit patterns)
@@ -301,7 +301,10 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         // dynamic smem: [par_h][par_w] parent pixels (128-byte aligned for TMA), then the horizontal pass
         // (offset arithmetic on s_dyn, not on a generic address, so that the accesses stay LDS/STS)
         uint8_t* s_par = s_dyn + ((128u - ((uint32_t)__cvta_generic_to_shared(s_dyn) & 127u)) & 127u);
-        uint16_t* s_v = (uint16_t*)(s_par + (size_t)plan.par_h * PW);   // [RAW_H][par_w] vertical pass (8.8 fixed point)
+        // [RAW_H][par_w] vertical pass (8.8 fixed point): dead before the Gaussian row pass writes s_row, so it
+        // lives there when it fits (always at the reference's scale 1.2) and the CTA stays under 1/6 of the SM
+        uint16_t* s_v = (size_t)RAW_H * PW * sizeof(uint16_t) <= sizeof(s_row) ? (uint16_t*)s_row
+                                                                               : (uint16_t*)(s_par + (size_t)plan.par_h * PW);
         // bounding box of the parent pixels this tile reads (host-computed per tile column / row)
         const uint32_t bx = __ldg(tab + L.bndx_off + blockIdx.x), by = __ldg(tab + L.bndy_off + blockIdx.y);
         const int px_lo = (int)(bx & 0xffff), px_hi = (int)(bx >> 16), py0 = (int)(by & 0xffff);
@@ -596,7 +599,8 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
 
 size_t vs_level_dyn_smem(const VsPlan& p)
 {
-    return 128 + (size_t)p.par_h * p.par_w + (size_t)RAW_H * p.par_w * sizeof(uint16_t);
+    const size_t v = (size_t)RAW_H * p.par_w * sizeof(uint16_t);
+    return 128 + (size_t)p.par_h * p.par_w + (v <= sizeof(float) * BL_ROWS * VS_TW ? 0 : v);
 }
 
 int vs_configure_level_smem(const VsPlan& p)
