@@ -5,6 +5,7 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-i
 rows = list(csv.reader(out.splitlines()))
 hdr = rows[1]; data = rows[2:]
 iS, iE, iSamp = hdr.index('Source'), hdr.index('Instructions Executed'), hdr.index('# Samples')
+data = [r for r in data if len(r) > max(iE, iSamp) and r[iE].isdigit()]
 tot = sum(int(r[iE]) for r in data); ts = sum(int(r[iSamp]) for r in data)
 print('total warp inst', tot, 'samples', ts, 'winst/px %.3f' % (tot / px))
 seg = acc = sacc = start = 0
