@@ -26,7 +26,7 @@
 
 #define RAW_W (VS_TW + 2 * VS_HALO)   // 72 columns: x0-4 .. x0+67
 #define RAW_H (VS_TH + 2 * VS_HALO)   // 38 rows:    y0-4 .. y0+33
-#define RAW_S 80                      // row stride of the 16-bit tile (elements)
+#define RAW_S 84                      // row stride of the 16-bit tile (elements): 42 words, so a column of words spreads over 16 banks
 #define SC_H (VS_TH + 2)              // score rows  y0-1 .. y0+TH
 #define SC_S 72                       // score row stride; column index = tx + 4
 #define BL_ROWS (VS_TH + 6)
@@ -455,21 +455,26 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             }
             *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(0u, 0u);
         }
-        // one warp-aggregated push of (row, word) entries for the four masks
+        // one warp-aggregated push of (row, word) entries for the four masks, in row-major order (lane = word pair
+        // of row r0 or r0 + 1: pair A then pair B per lane, rows r0 + 16 after): a warp of the network pass then
+        // reads runs of neighbouring words of one row instead of every second word of two rows -- half the bank
+        // conflicts of the 20 loads per queued pair
         uint32_t mk[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) mk[j] = __ballot_sync(0xffffffffu, need[j] != 0);
-        const int c0 = __popc(mk[0]), c1 = __popc(mk[1]), c2 = __popc(mk[2]), c3 = __popc(mk[3]);
-        if (c0 + c1 + c2 + c3) {
+        const int c01 = __popc(mk[0]) + __popc(mk[1]), c23 = __popc(mk[2]) + __popc(mk[3]);
+        if (c01 + c23) {
             int basepos = 0;
-            if (lane == 0) basepos = smem_atomic_add(&s_nq, c0 + c1 + c2 + c3);
+            if (lane == 0) basepos = smem_atomic_add(&s_nq, c01 + c23);
             basepos = __shfl_sync(0xffffffffu, basepos, 0);
             const uint32_t lt = (1u << lane) - 1u;
             const int r0 = tid >> 4;
-            if (need[0]) s_queue[basepos + __popc(mk[0] & lt)] = (uint16_t)((r0 << 6) | (2 * w + 2));
-            if (need[1]) s_queue[basepos + c0 + __popc(mk[1] & lt)] = (uint16_t)((r0 << 6) | (2 * w + 3));
-            if (need[2]) s_queue[basepos + c0 + c1 + __popc(mk[2] & lt)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 2));
-            if (need[3]) s_queue[basepos + c0 + c1 + c2 + __popc(mk[3] & lt)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 3));
+            const int p01 = basepos + __popc(mk[0] & lt) + __popc(mk[1] & lt);
+            const int p23 = basepos + c01 + __popc(mk[2] & lt) + __popc(mk[3] & lt);
+            if (need[0]) s_queue[p01] = (uint16_t)((r0 << 6) | (2 * w + 2));
+            if (need[1]) s_queue[p01 + (need[0] != 0)] = (uint16_t)((r0 << 6) | (2 * w + 3));
+            if (need[2]) s_queue[p23] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 2));
+            if (need[3]) s_queue[p23 + (need[2] != 0)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 3));
         }
     }
     if (tid >= 256 - 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
