@@ -133,6 +133,9 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
 int vs_launch_bgr2gray(const uint8_t* d_bgr, uint8_t* d_gray, size_t n_pixels, cudaStream_t s);
 int vs_configure_octree_smem(void);
 int vs_launch_octree(vslam_orb* o, int batch, cudaStream_t s);
+struct CUtensorMap_st;
+bool vs_image_tensor_map(struct CUtensorMap_st* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
+                         int frames, int box_w, int box_h);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
 int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,

@@ -639,17 +639,18 @@ static vs_encode_tiled_fn vs_encode_tiled()
     return fn;
 }
 
-// Tensor map of a parent image stack uint8 [frames][h][pitch] with a (par_w, par_h, 1) box.  Returns false
-// when TMA cannot describe it (unaligned base / strides, box too large); the kernel then stages by hand.
-static bool vs_parent_tensor_map(CUtensorMap* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
-                                 int frames, const VsPlan& p)
+// Tensor map of an image stack uint8 [frames][h][pitch] with a (box_w, box_h, 1) box.  Returns false when TMA
+// cannot describe it (unaligned base / strides, box too large); the kernels then stage by hand.  A box must start
+// on a 16-byte boundary of the innermost dimension (an unaligned x faults with "illegal instruction").
+bool vs_image_tensor_map(struct CUtensorMap_st* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
+                         int frames, int box_w, int box_h)
 {
     vs_encode_tiled_fn enc = vs_encode_tiled();
-    if (!enc || p.par_w > 256 || p.par_h > 256 || (p.par_w & 15)) return false;
+    if (!enc || box_w > 256 || box_h > 256 || (box_w & 15) || w <= 0 || h <= 0 || frames <= 0) return false;
     if (((uintptr_t)base & 15) || (pitch & 15) || (frame_stride & 15)) return false;
     const cuuint64_t gdim[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
     const cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
-    const cuuint32_t box[3] = {(cuuint32_t)p.par_w, (cuuint32_t)p.par_h, 1u};
+    const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -668,10 +669,11 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
         memset(&tm, 0, sizeof(tm));
         int use_tma = 0;
         if (l == 1)
-            use_tma = vs_parent_tensor_map(&tm, d_frames, p.width, p.height, (size_t)pitch, (size_t)pitch * p.height, batch, p);
+            use_tma = vs_image_tensor_map(&tm, d_frames, p.width, p.height, (size_t)pitch, (size_t)pitch * p.height, batch,
+                                          p.par_w, p.par_h);
         else if (l > 1)
-            use_tma = vs_parent_tensor_map(&tm, o->d_pyr + p.lv[l - 1].raw_off, p.lv[l - 1].w, p.lv[l - 1].h,
-                                           (size_t)p.lv[l - 1].pitch, p.pyr_frame_bytes, batch, p);
+            use_tma = vs_image_tensor_map(&tm, o->d_pyr + p.lv[l - 1].raw_off, p.lv[l - 1].w, p.lv[l - 1].h,
+                                          (size_t)p.lv[l - 1].pitch, p.pyr_frame_bytes, batch, p.par_w, p.par_h);
         dim3 grid(L.tiles_x, L.tiles_y, batch);
         vs_prof_mark(o, l, s);
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);

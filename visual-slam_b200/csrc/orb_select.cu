@@ -7,6 +7,9 @@
 //   vs_describe_kernel one warp per keypoint: intensity-centroid angle with cv::fastAtan2's
 //                      polynomial (K6), keypoint record, steered rBRIEF on the blurred level (K7b)
 // All of this restates what cv2.ORB.detectAndCompute does behind extractor.py:65.
+#include <cuda.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "brief.cuh"
 
@@ -488,6 +491,204 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
     }
 }
 
+// ---------------------------------------------------------------------------
+// The same kernel with both windows staged by TMA (cp.async.bulk.tensor.3d over (x, y, frame), one instruction per
+// window issued by one lane).  The hand-staged kernel above is bound by the LSU data pipe (85 % busy: ~135 of its
+// ~200 wavefronts per keypoint are the LDGSTS copies); TMA writes shared memory through the async proxy and takes
+// that traffic off the pipe.  A TMA box must start on a 16-byte boundary of x, so a window carries up to 15 bytes of
+// slack per row: the unblurred patch is a 31 x 48-byte box (lane = row reads it as three 128-bit words, conflict-free
+// at that stride, and picks its nine words by the warp-uniform word offset), the blurred one 37 x 64 bytes.  The
+// unblurred windows are double-buffered: lane k looks keypoint k up at the start and issues its loads when a buffer
+// frees, so the load of keypoint k + 1 flies while k's centroid is reduced.
+#define TD_RAW_W 48
+#define TD_RAW_BYTES 1536                 // 31 rows x 48 B = 1488, padded to the 128-byte TMA destination alignment
+#define TD_BLUR_W 64
+#define TD_BLUR_BYTES 2432                // 37 rows x 64 B = 2368, padded likewise
+struct alignas(128) VsDescMaps {
+    CUtensorMap raw[8], blur[8];          // per level; raw[0] is the caller's frame stack
+};
+
+__device__ __forceinline__ void td_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n .reg .pred p;\n"
+        "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra D%=;\n bra W%=;\n"
+        "D%=:\n}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+
+__device__ __forceinline__ void td_load(uint32_t dst, const CUtensorMap* tm, int x, int y, int b, uint32_t bar, uint32_t bytes)
+{
+    // the window was last read through the generic proxy: order those reads before the async-proxy write
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"((uint64_t)tm), "r"(x), "r"(y), "r"(b), "r"(bar) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 5)
+vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constant__ VsDescMaps maps,
+                       const VsCand* __restrict__ stage, const int32_t* __restrict__ counters,
+                       vslam_keypoint* __restrict__ kp_out, uint8_t* __restrict__ desc_out, int32_t* __restrict__ count_out)
+{
+    __shared__ __align__(128) uint8_t s_blur[8][TD_BLUR_BYTES];
+    __shared__ __align__(128) uint8_t s_raw[8][2][TD_RAW_BYTES];
+    __shared__ __align__(8) unsigned long long s_bar[8][3];      // per warp: raw buffer 0 / 1, blurred window
+    const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int32_t* ctr = counters + (size_t)b * plan.n_levels * VS_CTR_STRIDE;
+    __shared__ int s_start[VS_MAX_LEVELS + 1];
+    if (threadIdx.x < 32) {
+        const int l = threadIdx.x;
+        int n = l < plan.n_levels ? ctr[l * VS_CTR_STRIDE + VS_CTR_NFINAL] : 0, incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (l >= o) incl += t;
+        }
+        if (l <= VS_MAX_LEVELS) s_start[l] = incl - n;          // s_start[n_levels..] = total
+    }
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[wid][0]);
+    if (lane == 0) {
+        for (int k = 0; k < 3; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * k));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const int total = s_start[plan.n_levels];
+    if (blockIdx.x == 0 && threadIdx.x == 0) count_out[b] = total;
+    uint8_t* wb = s_blur[wid];
+    const uint32_t wb_u = (uint32_t)__cvta_generic_to_shared(wb);
+    const uint32_t wr_u = (uint32_t)__cvta_generic_to_shared(&s_raw[wid][0][0]);
+
+    // disc mask of this lane's patch row (pass A): byte k of word j <-> u = 4j + k - 15
+    uint32_t ic_mask[8];
+    {
+        const int v = lane - VS_HALF_PATCH;
+        const int hw = lane < IC_WIN ? c_umax[v < 0 ? -v : v] : -1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            uint32_t mk = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int uu = 4 * j + k - VS_HALF_PATCH;
+                if ((uu < 0 ? -uu : uu) <= hw) mk |= 255u << (8 * k);
+            }
+            ic_mask[j] = mk;
+        }
+    }
+    const int i0 = (blockIdx.x * 8 + wid) * VS_DESC_PER_WARP;
+    const int nk = min(VS_DESC_PER_WARP, min(total, plan.kp_cap) - i0);   // warp-uniform; <= 0: nothing to do
+    if (nk <= 0) return;
+    // lane k < nk looks up keypoint k: level, level coordinates, response, pattern centre
+    int m_level = 0, m_x = 0, m_y = 0, m_cx = 0, m_cy = 0;
+    uint32_t m_resp = 0;
+    float m_scale = 1.f;
+    if (lane < nk) {
+        const int i = i0 + lane;
+        while (m_level + 1 < plan.n_levels && i >= s_start[m_level + 1]) ++m_level;
+        const VsLevel& L = plan.lv[m_level];
+        const VsCand c = stage[(size_t)b * plan.stage_frame_entries + L.stage_off + (i - s_start[m_level])];
+        m_x = c.x; m_y = c.y; m_resp = c.v; m_scale = L.scale;
+        // centre of the rBRIEF pattern: cvRound(pt * (1/scale))
+        const float inv = __fdiv_rn(1.f, L.scale);
+        m_cx = __float2int_rn(__fmul_rn(__fmul_rn((float)m_x, L.scale), inv));
+        m_cy = __float2int_rn(__fmul_rn(__fmul_rn((float)m_y, L.scale), inv));
+        // the first loads: unblurred windows of keypoints 0 and 1, blurred window of keypoint 0
+        if (lane < 2) td_load(wr_u + lane * TD_RAW_BYTES, &maps.raw[m_level], (m_x - VS_HALF_PATCH) & ~15, m_y - VS_HALF_PATCH, b,
+                              bar0 + 8 * lane, TD_RAW_W * IC_WIN);
+        if (lane == 0) td_load(wb_u, &maps.blur[m_level], (m_cx - DESC_R) & ~15, m_cy - DESC_R, b, bar0 + 16, TD_BLUR_W * DESC_WIN);
+    }
+    // Pass A: intensity-centroid angles, one keypoint after the other (lane k keeps keypoint k's angle)
+    float m_ang = 0.f;
+    for (int k = 0; k < nk; ++k) {
+        const int px0 = __shfl_sync(0xffffffffu, m_x, k) - VS_HALF_PATCH;     // first column of the patch
+        td_wait(bar0 + 8 * (k & 1), (uint32_t)(k >> 1) & 1u);
+        int m10 = 0, m01 = 0;
+        if (lane < IC_WIN) {
+            const uint4* p4 = (const uint4*)(&s_raw[wid][k & 1][0] + lane * TD_RAW_W);
+            const uint4 a = p4[0], c4 = p4[1], e = p4[2];
+            const uint32_t r[12] = {a.x, a.y, a.z, a.w, c4.x, c4.y, c4.z, c4.w, e.x, e.y, e.z, e.w};
+            uint32_t w[9];
+            switch ((px0 & 15) >> 2) {
+            case 0:
+#pragma unroll
+                for (int j = 0; j < 9; ++j) w[j] = r[j];
+                break;
+            case 1:
+#pragma unroll
+                for (int j = 0; j < 9; ++j) w[j] = r[j + 1];
+                break;
+            case 2:
+#pragma unroll
+                for (int j = 0; j < 9; ++j) w[j] = r[j + 2];
+                break;
+            default:
+#pragma unroll
+                for (int j = 0; j < 9; ++j) w[j] = r[j + 3];
+                break;
+            }
+            const int sh = (px0 & 3) * 8;
+            int rs = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t q = __funnelshift_r(w[j], w[j + 1], sh) & ic_mask[j];
+                // bytes of word j <-> u = 4j-15 .. 4j-12
+                const uint32_t wu = (uint32_t)((4 * j - 15) & 255) | ((uint32_t)((4 * j - 14) & 255) << 8) |
+                                    ((uint32_t)((4 * j - 13) & 255) << 16) | ((uint32_t)((4 * j - 12) & 255) << 24);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(q), "r"(wu));
+                rs = (int)__dp4a(q, 0x01010101u, (uint32_t)rs);
+            }
+            m01 = (lane - VS_HALF_PATCH) * rs;
+        }
+        __syncwarp();
+        if (lane == k + 2 && lane < nk)       // the buffer is free again: keypoint k + 2's window
+            td_load(wr_u + (k & 1) * TD_RAW_BYTES, &maps.raw[m_level], (m_x - VS_HALF_PATCH) & ~15, m_y - VS_HALF_PATCH, b,
+                    bar0 + 8 * (k & 1), TD_RAW_W * IC_WIN);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        }
+        const float ang = fast_atan2_deg((float)m01, (float)m10);
+        if (lane == k) {
+            m_ang = ang;
+            vslam_keypoint* ko = kp_out + (size_t)b * plan.kp_cap + i0 + k;
+            ko->x = __fmul_rn((float)m_x, m_scale); ko->y = __fmul_rn((float)m_y, m_scale); ko->size = __fmul_rn(31.f, m_scale);
+            ko->angle = ang; ko->response = __uint_as_float(m_resp); ko->octave = m_level;
+        }
+    }
+    // rotation from the angle in radians (K7b): (float)cos / (float)sin of the float32 angle, evaluated in double
+    float m_ca, m_sa;
+    {
+        const float rad = __fmul_rn(m_ang, (float)(3.14159265358979323846 / 180.f));
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        m_ca = (float)cd; m_sa = (float)sd;
+    }
+    // Pass B: steered rBRIEF on the blurred window
+    for (int k = 0; k < nk; ++k) {
+        const float ca = __shfl_sync(0xffffffffu, m_ca, k), sa = __shfl_sync(0xffffffffu, m_sa, k);
+        const int bx0 = __shfl_sync(0xffffffffu, m_cx, k) - DESC_R;           // first column of the window
+        td_wait(bar0 + 16, (uint32_t)k & 1u);
+        // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
+        const float magic = 12582912.0f;
+        const uint32_t off0 = (uint32_t)(DESC_R * TD_BLUR_W + DESC_R + (bx0 & 15)) - 0x4B400000u * (TD_BLUR_W + 1);
+        uint32_t byte = 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            const float4 p = __ldg(&g_patf_t[t * 32 + lane]);
+            const float fx0 = __fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), fy0 = __fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca));
+            const float fx1 = __fsub_rn(__fmul_rn(p.z, ca), __fmul_rn(p.w, sa)), fy1 = __fadd_rn(__fmul_rn(p.z, sa), __fmul_rn(p.w, ca));
+            const uint32_t i0w = __float_as_uint(__fadd_rn(fy0, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
+            const uint32_t i1w = __float_as_uint(__fadd_rn(fy1, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
+            byte |= (uint32_t)(wb[i0w] < wb[i1w]) << t;
+        }
+        __syncwarp();
+        if (lane == k + 1 && lane < nk)
+            td_load(wb_u, &maps.blur[m_level], (m_cx - DESC_R) & ~15, m_cy - DESC_R, b, bar0 + 16, TD_BLUR_W * DESC_WIN);
+        desc_out[((size_t)b * plan.kp_cap + i0 + k) * 32 + lane] = (uint8_t)byte;
+    }
+}
+
 void vs_configure_select_smem(int bytes)
 {
     if (bytes > 48 * 1024)
@@ -518,8 +719,25 @@ int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
     }
     vs_prof_mark(o, VS_PROF_DESCRIBE, s);
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    vs_describe_kernel<<<dim3((p.kp_cap + 8 * VS_DESC_PER_WARP - 1) / (8 * VS_DESC_PER_WARP), batch), 256, 0, s>>>(
-        p, d_frames, pitch, fstride, o->d_pyr, o->d_stage, o->d_counters, d_kp, d_desc, d_count);
+    // both windows by TMA when every level's images can be described by a tensor map (16-byte aligned base and
+    // pitches: always for the pyramid, for the caller's frames when they are aligned), else the hand-staged kernel
+    VsDescMaps maps;
+    bool tma = p.n_levels <= 8 && getenv("VSLAM_DESCRIBE_NO_TMA") == nullptr;
+    for (int l = 0; tma && l < p.n_levels; ++l) {
+        const VsLevel& L = p.lv[l];
+        if (L.w <= 0 || L.h <= 0) { memset(&maps.raw[l], 0, sizeof(CUtensorMap)); memset(&maps.blur[l], 0, sizeof(CUtensorMap)); continue; }
+        tma = l == 0 ? vs_image_tensor_map(&maps.raw[0], d_frames, p.width, p.height, (size_t)pitch, fstride, batch, TD_RAW_W, IC_WIN)
+                     : vs_image_tensor_map(&maps.raw[l], o->d_pyr + L.raw_off, L.w, L.h, (size_t)L.pitch, p.pyr_frame_bytes, batch,
+                                           TD_RAW_W, IC_WIN);
+        tma = tma && vs_image_tensor_map(&maps.blur[l], o->d_pyr + L.blur_off, L.w, L.h, (size_t)L.pitch, p.pyr_frame_bytes, batch,
+                                         TD_BLUR_W, DESC_WIN);
+    }
+    const dim3 dgrid((p.kp_cap + 8 * VS_DESC_PER_WARP - 1) / (8 * VS_DESC_PER_WARP), batch);
+    if (tma)
+        vs_describe_tma_kernel<<<dgrid, 256, 0, s>>>(p, maps, o->d_stage, o->d_counters, d_kp, d_desc, d_count);
+    else
+        vs_describe_kernel<<<dgrid, 256, 0, s>>>(p, d_frames, pitch, fstride, o->d_pyr, o->d_stage, o->d_counters, d_kp,
+                                                  d_desc, d_count);
     vs_prof_mark(o, -1, s);
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
