@@ -342,7 +342,7 @@ __device__ __forceinline__ void stage_window(uint8_t* win, const uint8_t* img, i
 
 // One warp per keypoint, VS_DESC_PER_WARP keypoints in turn.  Keypoints are at least 31 px inside
 // their level, so both windows lie inside the image.
-#define VS_DESC_PER_WARP 4
+#define VS_DESC_PER_WARP 8
 
 __global__ void __launch_bounds__(256)
 vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frames, int fpitch,
