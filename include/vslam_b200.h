@@ -184,6 +184,20 @@ int vslam_bf_knn2_hamming256(const uint8_t* d_query, int nq, long q_stride_rows,
 int vslam_bf_knn2_hamming256_host(const uint8_t* h_query, int nq, const uint8_t* h_train,
                                   int nt, int32_t* h_idx, int32_t* h_dist);
 
+/* No counterpart in the reference: added for callers that
+ * cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * kNN-2 of ONE descriptor-set pair with the outputs of vslam_bf_knn2_hamming256 (d_idx / d_dist
+ * int32 [nq][2], same tie rule), computed by the split-train XOR + POPC kernel with its partial
+ * results in a static __device__ array of the library (2 MiB, held by every GPU that loads the
+ * library until exit) -- the call makes no cudaMalloc / cudaFree / allocating library call.
+ * Limit: nq <= VSLAM_NOALLOC_MAX_QUERY (VSLAM_E_CAPACITY beyond, nothing launched); nt is unlimited.
+ * All calls share the scratch: calls that overlap on the GPU (two streams) race -- serialise them.
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress); make one call
+ * before starting a graph capture. */
+#define VSLAM_NOALLOC_MAX_QUERY 8192
+int vslam_bf_knn2_hamming256_noalloc(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt,
+                                     int32_t* d_idx, int32_t* d_dist, void* stream);
+
 /* Replaces the Lowe ratio loop of DescriptorMatcher.match (matcher.py:73-81):
  * keep row q iff two neighbours exist and (!ratio_test or
  * (double)(float)d1 < ratio*(double)(float)d2), or exactly one neighbour exists.
