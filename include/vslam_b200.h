@@ -244,9 +244,13 @@ int vslam_score_essential_host(const double* h_E, const double* h_K, const float
                                const float* h_p2, int n, double thr, uint8_t* h_mask,
                                int* n_inliers);
 /* Replaces cv2.findFundamentalMat(p1, p2, FM_RANSAC, thr, conf) (matcher.py:192):
- * 7-point hypotheses from a seeded counter-based sampler evaluated in parallel,
- * winner = the most inliers (lowest hypothesis id on ties) within the adaptive
- * iteration horizon.  h_F receives the winning minimal solution scaled to F[8] = 1. */
+ * 7-point hypotheses evaluated in parallel on the subsets OpenCV itself draws (its RNG(-1)
+ * stream with duplicate and collinearity rejection), winner and stopping point by a replay of
+ * its sequential loop, so the mask is the one cv2 returns; below 15 points cv2 runs LMedS
+ * and so does this call.  h_F receives the winning minimal solution scaled to F[8] = 1
+ * (all zeros when there is no model).  `seed` (here and below): 0 = OpenCV's own stream --
+ * what the reference runs, cv2's estimators ignore cv2.setRNGSeed; any other value selects
+ * another deterministic stream. */
 int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p2, int n, double thr,
                                   double conf, int max_iters, uint64_t seed, double* h_F,
                                   uint8_t* h_mask, int* n_inliers);

@@ -2,11 +2,12 @@
 oracle and the golden vectors produced by the reference (cv2 4.13).
 
 Bars: scoring masks exact given the reference's own F / E; pose: identical winner, mask equal
-to the oracle's, R / t within 1e-6; triangulation rel 1e-4 on xyz/w; full estimators
-(our own seeded sampler, so a different hypothesis stream than cv2's RNG): inlier-set Jaccard
-against cv2's mask no worse than cv2 agrees with ITSELF when its input order is permuted
-(measured in the build container over 8 permutations of the same three fixtures:
-F thr 3: 0.942-0.968, E thr 1: 0.82-0.86, E thr 3: 0.991) and at least 97 % of cv2's inlier count.
+to the oracle's, R / t within 1e-6; triangulation rel 1e-4 on xyz/w; full estimators: the kernels
+draw OpenCV's own sample stream (cv::RNG(-1), duplicate / collinearity rejection) and replay its
+adaptive stop, so the inlier MASK equals the reference's -- exactly on every golden case but one:
+pair12 at E threshold 1, where cv2's winning root is itself inexact (it violates the cubic
+constraints of an essential matrix by 5e-5; the polished root has 1253 inliers to cv2's 1252), held to
+Jaccard >= 0.998 and |count difference| <= 1.  F to 1e-9, E to 1e-7 (up to sign).
 """
 import numpy as np
 import pytest
@@ -73,29 +74,82 @@ def test_recover_pose_and_triangulate(name, tag, K):
     assert np.allclose(a, o[:3] / o[3], rtol=1e-4, atol=1e-4 * np.abs(b).max())
 
 
+def _same_up_to_sign(A, B, tol):
+    A, B = A / np.linalg.norm(A), B / np.linalg.norm(B)
+    return min(np.abs(A - B).max(), np.abs(A + B).max()) <= tol
+
+
 @pytest.mark.parametrize("name,tag,K", CASES)
-def test_ransac_estimators_agree_with_reference(name, tag, K):
+def test_ransac_estimators_equal_reference(name, tag, K):
     from orbslam2 import utils
     g = load_golden(name)
     p1, p2 = g[tag + "_p1"], g[tag + "_p2"]
     F, mask = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)
-    ref = g[tag + "_Fmask"]
     assert F.shape == (3, 3) and abs(F[2, 2] - 1.0) < 1e-12 and mask.shape == (len(p1), 1)
-    assert _jaccard(mask, ref) >= 0.93, _jaccard(mask, ref)
-    assert int(mask.sum()) >= 0.97 * int(ref.sum())
-    assert abs(np.linalg.det(F)) < 1e-6 * np.abs(F).max() ** 3 + 1e-12            # rank 2
+    assert np.array_equal(mask.ravel(), g[tag + "_Fmask"])                          # the reference's own mask
+    assert np.abs(F - g[tag + "_F"]).max() <= 1e-9 * max(1.0, np.abs(g[tag + "_F"]).max())
     assert np.array_equal(utils.score_fundamental(F, p1, p2, 3.0), mask.ravel())   # mask belongs to the returned F
-    F2, mask2 = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)                   # deterministic for a seed
+    F2, mask2 = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)                   # deterministic
     assert np.array_equal(F, F2) and np.array_equal(mask, mask2)
+    F3, mask3 = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99, seed=12345)       # another seed: another stream
+    assert F3.shape == (3, 3) and _jaccard(mask3, mask) > 0.9
     for thr in (1.0, 3.0):
         E, emask = utils.calculate_essential_matrix(p1, p2, K, prob=0.999, threshold=thr)
         ref = g["%s_Emask_%d" % (tag, int(thr))]
-        jac = _jaccard(emask, ref)
-        assert jac >= (0.97 if thr == 3.0 else 0.80), (thr, jac, int(emask.sum()), int(ref.sum()))
-        assert int(emask.sum()) >= 0.97 * int(ref.sum())
+        if (tag, thr) == ("pair12", 1.0):       # cv2's own root is inexact here (module docstring)
+            assert _jaccard(emask, ref) >= 0.998 and abs(int(emask.sum()) - int(ref.sum())) <= 1
+        else:
+            assert np.array_equal(emask.ravel(), ref), (thr, int(emask.sum()), int(ref.sum()))
+            assert _same_up_to_sign(E, g["%s_E_%d" % (tag, int(thr))], 1e-7)
         s = np.linalg.svd(E, compute_uv=False)
-        assert abs(s[0] - s[1]) < 1e-6 and s[2] < 1e-6 and abs(s[0] - np.sqrt(0.5)) < 1e-6
+        assert abs(s[0] - s[1]) < 1e-9 and s[2] < 1e-9 and abs(s[0] - np.sqrt(0.5)) < 1e-9
         assert np.array_equal(utils.score_essential(E, p1, p2, K, thr), emask.ravel())
+
+
+def test_ransac_long_runs_equal_reference():
+    """24 synthetic scenes with 30..95 % inliers (tens to hundreds of RANSAC iterations each), golden masks made
+    by the reference's filter_matches_by_fundamental / calculate_essential_matrix (tests/golden/make_ransac_golden.py):
+    the sample stream, every minimal solution and the adaptive stop have to agree for the masks to be equal."""
+    from orbslam2 import utils
+    g = load_golden("ransac_cases.npz")
+    K = g["K"]
+    for s in range(int(g["n_scenes"])):
+        p1, p2 = g["s%02d_p1" % s], g["s%02d_p2" % s]
+        F, mask = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)
+        assert np.array_equal(mask.ravel(), g["s%02d_Fmask" % s]), ("F", s, int(mask.sum()), int(g["s%02d_Fmask" % s].sum()))
+        assert np.abs(F - g["s%02d_F" % s]).max() <= 1e-8 * max(1.0, np.abs(g["s%02d_F" % s]).max())
+        for thr in (1, 3):
+            E, emask = utils.calculate_essential_matrix(p1, p2, K, prob=0.999, threshold=float(thr))
+            ref = g["s%02d_Emask_%d" % (s, thr)]
+            assert np.array_equal(emask.ravel(), ref), ("E", s, thr, int(emask.sum()), int(ref.sum()))
+            assert _same_up_to_sign(E, g["s%02d_E_%d" % (s, thr)], 1e-6)
+
+
+def test_fundamental_below_15_points_runs_lmeds_like_cv2():
+    """cv2.findFundamentalMat(FM_RANSAC) runs LMedS for 8..14 points.  For n <= 13 the median error (element n // 2
+    of the sorted errors) is one of the 7 interpolated points, i.e. rounding noise around 1e-27, so WHICH exact fit
+    wins is not reproducible even in principle; what is: the result interpolates 7 of the points, those 7 are a subset
+    OpenCV's stream draws, and the mask is the sigma gate of that model.  At n = 14 the median is a real residual and
+    the mask has to equal the reference's."""
+    from oracle import geom_oracle as G
+    from orbslam2 import utils
+    g = load_golden("ransac_cases.npz")
+    for j in range(int(g["n_small"])):
+        p1, p2 = g["small%d_p1" % j], g["small%d_p2" % j]
+        n = len(p1)
+        F, mask = utils.find_fundamental_ransac(p1, p2, 3.0, 0.99)
+        assert mask.shape == (n, 1) and F is not None
+        err = G.fundamental_error(F, p1, p2)
+        seven = sorted(np.argsort(err)[:7].tolist())
+        assert err[seven].max() < 1e-12                                    # an un-refit minimal solution
+        niters = max(G.ransac_update_num_iters(0.99, 0.45, 7, 1000), 3)
+        rows = G.cv2_sample_table(p1, p2, 7, niters, True, max_attempts=1000)
+        assert any(sorted(r) == seven for r in rows)
+        med = float(np.sort(err)[n // 2])
+        sigma = max(2.5 * 1.4826 * (1 + 5.0 / (n - 7)) * np.sqrt(med), 0.001)
+        assert np.array_equal(mask.ravel() != 0, err <= np.float32(sigma * sigma))
+        if n == 14:
+            assert np.array_equal(mask.ravel(), g["small%d_Fmask" % j])
 
 
 def test_ransac_small_and_degenerate_inputs():

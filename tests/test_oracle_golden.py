@@ -126,6 +126,53 @@ def test_geometry_scoring_and_pose(name, tag, K):
     assert np.allclose(X[:3] / X[3], ref[:3] / ref[3], rtol=2e-3, atol=1e-4)   # float32 output of a 4x4 SVD
 
 
+@pytest.mark.parametrize("name,tag,K", [("synth640.npz", "s640", K_SYNTH), ("pair01.npz", "pair01", K_GERARD),
+                                        ("pair12.npz", "pair12", K_GERARD)])
+def test_ransac_replay_equals_reference_on_image_pairs(name, tag, K):
+    """oracle/geom_oracle.py restates OpenCV's RANSAC loop (RNG(-1) stream, subset rejection, adaptive stop): on the
+    reference's own outputs the replay returns the same mask, and the 7 points cv2's F interpolates are a row of
+    the generated subset table."""
+    from oracle import geom_oracle as G
+    g = load_golden(name)
+    p1, p2 = g[tag + "_p1"], g[tag + "_p2"]
+    F, mask, info = G.ransac_fundamental_cv2(p1, p2, 3.0, 0.99)
+    assert np.array_equal(mask, g[tag + "_Fmask"] != 0)
+    assert np.abs(F / F[2, 2] - g[tag + "_F"]).max() < 1e-9
+    x1 = np.c_[p1.astype(np.float64), np.ones(len(p1))]
+    x2 = np.c_[p2.astype(np.float64), np.ones(len(p1))]
+    seven = sorted(np.argsort(np.abs(np.einsum("ni,ij,nj->n", x2, g[tag + "_F"], x1)))[:7].tolist())
+    assert sorted(info["sample"]) == seven
+    for thr in (1, 3):
+        E, emask, _ = G.ransac_essential_cv2(p1, p2, K, 0.999, float(thr))
+        ref = g["%s_Emask_%d" % (tag, thr)] != 0
+        if (tag, thr) == ("pair12", 1):     # cv2's winning root is inexact here (cubic constraints off by 5e-5)
+            assert (emask & ref).sum() / (emask | ref).sum() >= 0.998 and abs(int(emask.sum()) - int(ref.sum())) <= 1
+        else:
+            assert np.array_equal(emask, ref)
+
+
+def test_ransac_replay_equals_reference_on_long_runs():
+    """The synthetic two-view goldens (tests/golden/make_ransac_golden.py, up to 1000 iterations each): F on all 24
+    scenes, E on the ones the pure-Python five-point solver finishes in a few seconds, LMedS at 14 points."""
+    from oracle import geom_oracle as G
+    g = load_golden("ransac_cases.npz")
+    K = g["K"]
+    for s in range(int(g["n_scenes"])):
+        p1, p2 = g["s%02d_p1" % s], g["s%02d_p2" % s]
+        F, mask, _ = G.ransac_fundamental_cv2(p1, p2, 3.0, 0.99)
+        assert np.array_equal(mask, g["s%02d_Fmask" % s] != 0), s
+    for s in (0, 8, 10, 12, 15, 18, 21):
+        p1, p2 = g["s%02d_p1" % s], g["s%02d_p2" % s]
+        for thr in (1, 3):
+            E, emask, _ = G.ransac_essential_cv2(p1, p2, K, 0.999, float(thr))
+            assert np.array_equal(emask, g["s%02d_Emask_%d" % (s, thr)] != 0), (s, thr)
+    for j in range(int(g["n_small"])):
+        p1, p2 = g["small%d_p1" % j], g["small%d_p2" % j]
+        if len(p1) == 14:
+            F, mask, _ = G.ransac_fundamental_cv2(p1, p2, 3.0, 0.99)
+            assert np.array_equal(mask, g["small%d_Fmask" % j] != 0)
+
+
 def test_orbslam2_oracle_invariants():
     """oracle/orbslam2_oracle.py (parity unpinned: the reference has no such mode): the quadtree keeps one
     corner per node, never more than quota + 3 nodes once past the first round, all of them when the quota

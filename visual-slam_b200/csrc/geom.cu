@@ -8,11 +8,13 @@
 // Scoring follows OpenCV's error functions exactly: F scores with
 // max(d1^2, d2^2) of the two point-to-epipolar-line distances, E with the Sampson error in
 // K-normalised coordinates; both in double, rounded to float and compared with (float)thr^2.
-// Hypotheses: every RANSAC iteration is one thread (7-point / 5-point minimal solver on a
-// sample drawn from a counter-based generator), every model is scored by one CTA, and the
-// OpenCV's sequential adaptive-termination rule is replayed over the per-model inlier counts (by one
-// thread of the batched F kernel, on the host for E), so the result is deterministic for a given seed.
+// Hypotheses: every RANSAC iteration is one thread (7-point / 5-point minimal solver) on the subset OpenCV itself
+// would draw at that iteration (geom_ransac.cuh: cv::RNG(-1) stream, duplicate / collinearity rejection), every model
+// is scored by one CTA / warp, and OpenCV's sequential adaptive-termination rule is replayed over the per-model inlier
+// counts (by one thread of the batched F kernel, on the host for E): the inlier mask is the reference's own
+// (tests/test_gpu_geometry.py: exact on 27 golden cases), not merely a mask of similar quality.
 #include <float.h>
+#include <limits.h>
 #include <math.h>
 
 #include <vector>
@@ -72,60 +74,18 @@ vs_score_models_kernel(const double* __restrict__ models, const int* __restrict_
 // Hartley normalisation of one point set: x' = (x - cx) * s
 struct Norm2 { double cx, cy, s; };
 
-__global__ void vs_ransac_f_hyp_kernel(const float2* __restrict__ p1, const float2* __restrict__ p2, int n,
-                                       Norm2 n1, Norm2 n2, uint64_t seed, int iters,
-                                       double* __restrict__ models, int* __restrict__ n_models)
-{
-    const int it = blockIdx.x * blockDim.x + threadIdx.x;
-    if (it >= iters) return;
-    int idx[7];
-    draw_sample<7>(seed, it, n, idx);
-    double x1[7][2], x2[7][2];
-    for (int j = 0; j < 7; ++j) {
-        float2 a = p1[idx[j]], b = p2[idx[j]];
-        x1[j][0] = (a.x - n1.cx) * n1.s; x1[j][1] = (a.y - n1.cy) * n1.s;
-        x2[j][0] = (b.x - n2.cx) * n2.s; x2[j][1] = (b.y - n2.cy) * n2.s;
-    }
-    double F[3][9];
-    const int nf = solve_7pt(x1, x2, F);
-    int kept = 0;
-    for (int k = 0; k < nf; ++k) {
-        // denormalise: F = T2^T Fn T1 with T = [s 0 -s cx; 0 s -s cy; 0 0 1]
-        const double* f = F[k];
-        double A[9];   // Fn * T1
-        for (int r = 0; r < 3; ++r) {
-            A[3 * r] = f[3 * r] * n1.s;
-            A[3 * r + 1] = f[3 * r + 1] * n1.s;
-            A[3 * r + 2] = f[3 * r + 2] - n1.s * (f[3 * r] * n1.cx + f[3 * r + 1] * n1.cy);
-        }
-        double G[9];   // T2^T * A
-        for (int c = 0; c < 3; ++c) {
-            G[c] = n2.s * A[c];
-            G[3 + c] = n2.s * A[3 + c];
-            G[6 + c] = A[6 + c] - n2.s * (n2.cx * A[c] + n2.cy * A[3 + c]);
-        }
-        bool ok = true;
-        for (int e = 0; e < 9; ++e) ok &= isfinite(G[e]);
-        if (!ok) continue;
-        const double mu = fabs(G[8]) > DBL_EPSILON ? 1.0 / G[8] : 1.0;    // F[2][2] = 1 as OpenCV's run7Point
-        double* out = models + ((size_t)it * 3 + kept) * 9;
-        for (int e = 0; e < 9; ++e) out[e] = G[e] * mu;
-        ++kept;
-    }
-    n_models[it] = kept;
-}
-
-__global__ void vs_ransac_e_hyp_kernel(const double2* __restrict__ p1, const double2* __restrict__ p2, int n,
-                                       uint64_t seed, int iters, double* __restrict__ models,
+// one thread per RANSAC iteration: the 5-point solver on the subset `table[it]` (drawn on the host from OpenCV's
+// stream: EMEstimatorCallback has no checkSubset, so the table depends on n alone)
+__global__ void vs_ransac_e_hyp_kernel(const double2* __restrict__ p1, const double2* __restrict__ p2,
+                                       const int* __restrict__ table, int iters, double* __restrict__ models,
                                        int* __restrict__ n_models)
 {
     const int it = blockIdx.x * blockDim.x + threadIdx.x;
     if (it >= iters) return;
-    int idx[5];
-    draw_sample<5>(seed, it, n, idx);
     double x1[5][2], x2[5][2];
     for (int j = 0; j < 5; ++j) {
-        double2 a = p1[idx[j]], b = p2[idx[j]];
+        const int i = table[it * 5 + j];
+        double2 a = p1[i], b = p2[i];
         x1[j][0] = a.x; x1[j][1] = a.y; x2[j][0] = b.x; x2[j][1] = b.y;
     }
     double E[10][9];
@@ -196,9 +156,12 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
                            double* __restrict__ out_F, uint8_t* __restrict__ out_mask, int32_t* __restrict__ out_ninl)
 {
     __shared__ double s_models[FB_R * 3 * 9];
-    __shared__ int s_nm[FB_R], s_counts[FB_R * 3];
+    __shared__ int s_nm[FB_R], s_counts[FB_R * 3], s_idx[FB_R * 7];
+    __shared__ float s_med[FB_R * 3];
     __shared__ double s_best[9], s_red[FB_THREADS / 32];
-    __shared__ int s_niters, s_maxgood, s_found, s_cnt;
+    __shared__ unsigned long long s_cursor;
+    __shared__ int s_niters, s_maxgood, s_found, s_cnt, s_fail;
+    __shared__ double s_minmed;
     const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = min(mcount ? mcount[pair] : cap, cap);
     float2* p1 = ws_pts + (size_t)pair * 2 * cap;
@@ -211,6 +174,9 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
         if (tid == 0) out_ninl[pair] = -1;
         return;
     }
+    // cv::findFundamentalMat: FM_RANSAC with fewer than 15 points silently runs the LMedS registrator instead
+    const bool lmeds = n < 15;
+    const uint32_t salt = vs_seed_salt(seed);
     // ---- matched points (kp == NULL: the caller placed them in ws_pts)
     if (match) {
         const vslam_keypoint* kq = kp_q + (size_t)pair * kp_cap;
@@ -223,7 +189,8 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
         }
         __syncthreads();
     }
-    // ---- Hartley normalisation: centroid, then mean distance to it
+    // ---- Hartley normalisation over all points: centroid, then mean distance to it.  (OpenCV's run7Point normalises
+    // the 7 sample points; the solutions of the 7-point problem do not depend on the coordinate frame.)
     double sx1 = 0, sy1 = 0, sx2 = 0, sy2 = 0;
     for (int i = tid; i < n; i += FB_THREADS) {
         const float2 a = p1[i], b = p2[i];
@@ -241,21 +208,30 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
     d1 = fb_block_sum(d1, s_red) / n; d2 = fb_block_sum(d2, s_red) / n;
     n1.s = d1 > 0 ? sqrt(2.0) / d1 : 1.0;
     n2.s = d2 > 0 ? sqrt(2.0) / d2 : 1.0;
-    if (tid == 0) { s_niters = max_iters; s_maxgood = 0; s_found = 0; }
+    if (tid == 0) {
+        // LMedS: a fixed horizon for 45 % outliers (LMeDSPointSetRegistrator::run), at least 3 iterations
+        s_niters = lmeds ? max(ransac_update_iters_dev(conf, 0.45, 7, max_iters), 3) : max_iters;
+        s_maxgood = 0; s_found = 0; s_cursor = 0ull; s_fail = INT_MAX; s_minmed = DBL_MAX;
+    }
     __syncthreads();
 
     for (int r0 = 0, R = FB_R0; r0 < s_niters; r0 += R, R = FB_R) {
+        // ---- the round's subsets from OpenCV's stream (warp 0); getSubset tries 10000 times for RANSAC, 1000 for LMedS
+        if (n > 7) {
+            if (wid == 0) cv_sample_round<7, true>(&s_cursor, salt, n, r0, R, s_idx, &s_fail, p1, p2, lmeds ? 1000 : 10000);
+        } else if (tid < R * 7) {
+            s_idx[tid] = tid % 7;         // exactly 7 points: the only subset
+        }
+        __syncthreads();
         // ---- hypotheses of iterations r0 .. r0 + R - 1, one thread each, spread evenly over the warps
         const int stride = FB_THREADS / R;
         if (tid % stride == 0) {
             const int j = tid / stride, it = r0 + j;
             int kept = 0;
-            if (it < max_iters) {
-                int idx[7];
-                draw_sample<7>(seed, it, n, idx);
+            if (it < max_iters && it < s_fail) {
                 double x1[7][2], x2[7][2];
                 for (int q = 0; q < 7; ++q) {
-                    const float2 a = p1[idx[q]], b = p2[idx[q]];
+                    const float2 a = p1[s_idx[j * 7 + q]], b = p2[s_idx[j * 7 + q]];
                     x1[q][0] = (a.x - n1.cx) * n1.s; x1[q][1] = (a.y - n1.cy) * n1.s;
                     x2[q][0] = (b.x - n2.cx) * n2.s; x2[q][1] = (b.y - n2.cy) * n2.s;
                 }
@@ -286,24 +262,46 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
             s_nm[j] = kept;
         }
         __syncthreads();
-        // ---- inlier counts: one warp per model slot
+        // ---- one warp per model slot: inlier count (RANSAC) or median error (LMedS, n <= 14: one point per lane)
         for (int slot = wid; slot < R * 3; slot += FB_THREADS / 32) {
             if (slot % 3 >= s_nm[slot / 3]) continue;
             const double* M = s_models + slot * 9;
-            int cnt = 0;
-            for (int i = lane; i < n; i += 32) {
-                const float2 a = p1[i], b = p2[i];
-                cnt += f_error(M, a.x, a.y, b.x, b.y) <= thr2;
+            if (!lmeds) {
+                int cnt = 0;
+                for (int i = lane; i < n; i += 32) {
+                    const float2 a = p1[i], b = p2[i];
+                    cnt += f_error(M, a.x, a.y, b.x, b.y) <= thr2;
+                }
+                for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+                if (lane == 0) s_counts[slot] = cnt;
+            } else {
+                // std::nth_element(err, err + n / 2, err + n): the (n / 2)-th smallest
+                float e = 0.f;
+                if (lane < n) { const float2 a = p1[lane], b = p2[lane]; e = f_error(M, a.x, a.y, b.x, b.y); }
+                int rank = 0;
+                for (int j = 0; j < n; ++j) {
+                    const float ej = __shfl_sync(0xffffffffu, e, j);
+                    rank += (ej < e) || (ej == e && j < lane);
+                }
+                if (lane < n && rank == n / 2) s_med[slot] = e;
+                if (lane < n && e != e) s_med[slot] = e;            // a NaN error poisons the comparison as in OpenCV
             }
-            for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
-            if (lane == 0) s_counts[slot] = cnt;
         }
         __syncthreads();
-        // ---- OpenCV's sequential loop over this round (cv::RANSACPointSetRegistrator::run)
+        // ---- OpenCV's sequential loop over this round (cv::RANSACPointSetRegistrator::run / LMeDS...::run)
         if (tid == 0) {
-            int niters = s_niters, max_good = s_maxgood;
+            int niters = min(s_niters, s_fail), max_good = s_maxgood;
             for (int j = 0; j < R && r0 + j < niters; ++j)
                 for (int k = 0; k < s_nm[j]; ++k) {
+                    if (lmeds) {
+                        const double med = (double)s_med[j * 3 + k];
+                        if (med < s_minmed) {
+                            s_minmed = med;
+                            for (int e = 0; e < 9; ++e) s_best[e] = s_models[(j * 3 + k) * 9 + e];
+                            s_found = 1;
+                        }
+                        continue;
+                    }
                     const int good = s_counts[j * 3 + k];
                     if (good > (max_good > 6 ? max_good : 6)) {
                         for (int e = 0; e < 9; ++e) s_best[e] = s_models[(j * 3 + k) * 9 + e];
@@ -323,19 +321,27 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
         if (tid == 0) out_ninl[pair] = 0;
         return;
     }
+    float t2 = thr2;
+    if (lmeds) {                 // sigma = 2.5 * 1.4826 * (1 + 5 / (n - 7)) * sqrt(minMedian), at least 0.001
+        double sigma = 2.5 * 1.4826 * (1 + 5. / (n - 7)) * sqrt(s_minmed);
+        sigma = fmax(sigma, 0.001);
+        t2 = (float)(sigma * sigma);
+    }
     if (tid == 0) s_cnt = 0;
     __syncthreads();
     int cnt = 0;
     for (int i = tid; i < n; i += FB_THREADS) {
         const float2 a = p1[i], b = p2[i];
-        const int in = f_error(s_best, a.x, a.y, b.x, b.y) <= thr2;
+        const int in = f_error(s_best, a.x, a.y, b.x, b.y) <= t2;
         mask[i] = (uint8_t)in;
         cnt += in;
     }
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
     if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
-    if (tid < 9) Fo[tid] = s_best[tid];
+    // LMedS reports failure (cv2 then returns F = None) when fewer than 7 points pass its own gate; the mask stands
     __syncthreads();
+    const bool have_F = !lmeds || s_cnt >= 7;
+    if (tid < 9) Fo[tid] = have_F ? s_best[tid] : 0.0;
     if (tid == 0) out_ninl[pair] = s_cnt;
 }
 
@@ -411,58 +417,53 @@ extern "C" int vslam_score_essential_host(const double* h_E, const double* h_K, 
     return score_common(1, h_E, a.p, b.p, n, (float)(t * t), h_mask, n_inliers);
 }
 
-static Norm2 hartley(const float* p, int n)
+// essential-matrix RANSAC: subsets from OpenCV's stream (host) -> hypotheses -> per-model counts -> sequential
+// replay of cv::RANSACPointSetRegistrator::run -> final mask
+static int ransac_e_driver(const void* d_p1, const void* d_p2, int n, float thr2, double conf, int max_iters,
+                           uint64_t seed, double* h_model, uint8_t* h_mask, int* n_inliers)
 {
-    double cx = 0, cy = 0;
-    for (int i = 0; i < n; ++i) { cx += p[2 * i]; cy += p[2 * i + 1]; }
-    cx /= n; cy /= n;
-    double d = 0;
-    for (int i = 0; i < n; ++i) d += hypot(p[2 * i] - cx, p[2 * i + 1] - cy);
-    d /= n;
-    Norm2 r = {cx, cy, d > 0 ? sqrt(2.0) / d : 1.0};
-    return r;
-}
-
-// shared driver: hypotheses -> per-model counts -> sequential replay -> final mask
-static int ransac_driver(int mode, const void* d_p1, const void* d_p2, int n, const float* h_p1, const float* h_p2,
-                         float thr2, double conf, int max_iters, uint64_t seed, double* h_model, uint8_t* h_mask,
-                         int* n_inliers)
-{
-    const int per = mode == 0 ? 3 : 10, mp = mode == 0 ? 7 : 5;
-    DevMem models, nm, counts;
+    const int per = 10, mp = 5;
+    // EMEstimatorCallback has no checkSubset: the subsets are a function of n alone
+    std::vector<int> table((size_t)max_iters * mp);
+    int n_rows = max_iters;
+    {
+        CvReader rd;
+        rd.init(0, vs_seed_salt(seed));
+        for (int it = 0; it < max_iters; ++it) {
+            if (n > mp) {
+                if (!cv_draw_subset<5, false>(rd, n, &table[(size_t)it * mp], nullptr, nullptr, 10000)) { n_rows = it; break; }
+            } else {
+                for (int j = 0; j < mp; ++j) table[(size_t)it * mp + j] = j;
+            }
+        }
+    }
+    if (n_inliers) *n_inliers = 0;
+    DevMem models, nm, counts, tab;
     GEOM_CUDA(models.alloc((size_t)max_iters * per * 9 * sizeof(double)));
     GEOM_CUDA(nm.alloc((size_t)max_iters * sizeof(int)));
     GEOM_CUDA(counts.alloc((size_t)max_iters * per * sizeof(int)));
-    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    if (mode == 0) {
-        Norm2 n1 = hartley(h_p1, n), n2 = hartley(h_p2, n);
-        vs_ransac_f_hyp_kernel<<<(max_iters + 63) / 64, 64>>>((const float2*)d_p1, (const float2*)d_p2, n, n1, n2, seed,
-                                                            max_iters, models.as<double>(), nm.as<int>());
-    } else {
-        vs_ransac_e_hyp_kernel<<<(max_iters + 31) / 32, 32>>>((const double2*)d_p1, (const double2*)d_p2, n, seed,
-                                                            max_iters, models.as<double>(), nm.as<int>());
-    }
+    GEOM_CUDA(tab.alloc(table.size() * sizeof(int)));
+    GEOM_CUDA(cudaMemcpy(tab.p, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemset(nm.p, 0, (size_t)max_iters * sizeof(int)));
+    __atomic_fetch_add(&g_vs_launches, 2ull, __ATOMIC_RELAXED);
+    vs_ransac_e_hyp_kernel<<<(n_rows + 31) / 32, 32>>>((const double2*)d_p1, (const double2*)d_p2, tab.as<int>(), n_rows,
+                                                      models.as<double>(), nm.as<int>());
     GEOM_CUDA(cudaGetLastError());
-    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    if (mode == 0)
-        vs_score_models_kernel<0><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
-                                                           counts.as<int>(), nullptr);
-    else
-        vs_score_models_kernel<1><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
-                                                           counts.as<int>(), nullptr);
+    vs_score_models_kernel<1><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
+                                                       counts.as<int>(), nullptr);
     GEOM_CUDA(cudaGetLastError());
     std::vector<int> h_counts((size_t)max_iters * per), h_nm(max_iters);
     GEOM_CUDA(cudaMemcpy(h_counts.data(), counts.p, h_counts.size() * sizeof(int), cudaMemcpyDeviceToHost));
     GEOM_CUDA(cudaMemcpy(h_nm.data(), nm.p, h_nm.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    h_nm.resize(n_rows);
     const int best = ransac_replay(h_counts, h_nm, per, n, mp, conf, max_iters);
-    if (n_inliers) *n_inliers = 0;
     if (best < 0) {
         for (int e = 0; e < 9; ++e) h_model[e] = 0.0;
         if (h_mask) memset(h_mask, 0, n);
         return VSLAM_OK;
     }
     GEOM_CUDA(cudaMemcpy(h_model, models.as<double>() + (size_t)best * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost));
-    return score_common(mode, h_model, d_p1, d_p2, n, thr2, h_mask, n_inliers);
+    return score_common(1, h_model, d_p1, d_p2, n, thr2, h_mask, n_inliers);
 }
 
 extern "C" size_t vslam_ransac_fundamental_batched_workspace(int pairs, int cap)
@@ -537,5 +538,5 @@ extern "C" int vslam_ransac_essential_host(const float* h_p1, const float* h_p2,
     GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
     GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
     double t = thr / ((h_K[0] + h_K[4]) / 2);
-    return ransac_driver(1, a.p, b.p, n, nullptr, nullptr, (float)(t * t), prob, max_iters, seed, h_E, h_mask, n_inliers);
+    return ransac_e_driver(a.p, b.p, n, (float)(t * t), prob, max_iters, seed, h_E, h_mask, n_inliers);
 }

@@ -58,22 +58,36 @@ VS_HD inline double poly_root_in(const double* q, int n, double xl, double xh, b
 // (the sign at infinity says whether a root is there).  Only real arithmetic, no start values, and the cost
 // follows the number of real roots (typically 2-6) -- the complex Durand-Kerner iteration this replaces spent
 // ~1600 instructions per sweep on all ten roots and often ran into its sweep limit.
-VS_HD inline int real_roots_deg10(const double* c, double* roots)
+VS_HD inline int real_roots_deg10(const double* c, double* roots, bool* deflated)
 {
-    const int N = 10;
+    const int NMAX = 10;
     double mx = 0.0;
-    for (int i = 0; i <= N; ++i) mx = fmax(mx, fabs(c[i]));
-    if (!(mx > 0.0) || fabs(c[N]) < 1e-13 * mx) return 0;
-    double a[N + 1];
-    for (int i = 0; i <= N; ++i) a[i] = c[i] / c[N];
+    for (int i = 0; i <= NMAX; ++i) mx = fmax(mx, fabs(c[i]));
+    *deflated = false;
+    if (!(mx > 0.0) || !isfinite(mx)) return 0;
+    // effective degree: leading coefficients that vanish against the largest one put roots at infinity (solutions
+    // with no component along the fourth basis vector -- pure sideways motion does that); the chain of derivatives
+    // below cannot bracket through critical points at 1e12, so those roots are dropped here and the caller is told
+    int N = NMAX;
+    while (N > 1 && fabs(c[N]) < 1e-11 * mx) --N;
+    *deflated = N < NMAX;
+    if (fabs(c[N]) < 1e-11 * mx) return 0;
+    // balance: x = s w with s = |c0 / cN|^(1/N) (the geometric mean of the root moduli), so that the scaled
+    // coefficients are of one order of magnitude whatever the unit of the roots is
+    double s = 1.0;
+    if (fabs(c[0]) > 0.0) s = exp((log(fabs(c[0])) - log(fabs(c[N]))) / N);
+    if (!(s > 1e-6 && s < 1e6)) s = 1.0;
+    double a[NMAX + 1], sp = 1.0;
+    for (int i = 0; i <= NMAX; ++i) { a[i] = i <= N ? c[i] * sp : 0.0; sp *= s; }
+    { const double lead = a[N]; for (int i = 0; i <= N; ++i) a[i] /= lead; }
     double B = 0.0;
     for (int i = 0; i < N; ++i) B = fmax(B, fabs(a[i]));
     B = fmin(1.0 + B, 1e8);                         // Cauchy bound; an essential matrix from |z| > 1e8 is degenerate anyway
-    double crit[N], next[N];
+    double crit[NMAX], next[NMAX];
     int nc = 0;                                     // real roots of the derivative one level up, ascending
     for (int m = N - 1; m >= 0; --m) {              // level m: q = m-th derivative (up to a positive factor), degree n
         const int n = N - m;
-        double q[N + 1];
+        double q[NMAX + 1];
         for (int i = 0; i <= n; ++i) {
             double f = a[i + m];
             for (int k = 0; k < m; ++k) f *= (double)(i + m - k);   // (i+m)! / i!
@@ -124,28 +138,139 @@ VS_HD inline int real_roots_deg10(const double* c, double* roots)
         nc = nr;
         for (int i = 0; i < nr; ++i) crit[i] = next[i];
     }
+    // back to the caller's unit at insertion
     int nout = 0;
     for (int k = 0; k < nc; ++k) {
-        const double x = crit[k];
+        const double x = crit[k] * s;
         bool dup = false;
-        for (int j = 0; j < nout; ++j) dup |= fabs(roots[j] - x) < 1e-9 * (1.0 + fabs(x));
+        for (int j = 0; j < nout; ++j) dup |= fabs(roots[j] - x) < 1e-9 * (s + fabs(x));
         if (!dup && isfinite(x)) roots[nout++] = x;
     }
     return nout;
 }
 
-// 5-point solver.  x1, x2: 5 correspondences in normalised camera coordinates.
-// Writes up to 10 essential matrices (row-major, x2^T E x1 = 0); returns the count.
-VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double E[10][9])
+// Residuals of the essential-matrix constraints at E (row-major): f[0..8] = 2 E E^T E - tr(E E^T) E, f[9] = det E.
+VS_HD inline void e_constraints(const double* E, double* f, double* EEt, double* tr_out)
 {
-    double A[5][9], nb[4][9];
-    for (int i = 0; i < 5; ++i) {
-        const double u = x1[i][0], v = x1[i][1], up = x2[i][0], vp = x2[i][1];
-        A[i][0] = up * u; A[i][1] = up * v; A[i][2] = up;
-        A[i][3] = vp * u; A[i][4] = vp * v; A[i][5] = vp;
-        A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            EEt[3 * i + j] = E[3 * i] * E[3 * j] + E[3 * i + 1] * E[3 * j + 1] + E[3 * i + 2] * E[3 * j + 2];
+    const double tr = EEt[0] + EEt[4] + EEt[8];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+            f[3 * i + j] = 2.0 * (EEt[3 * i] * E[j] + EEt[3 * i + 1] * E[3 + j] + EEt[3 * i + 2] * E[6 + j]) - tr * E[3 * i + j];
+    f[9] = det3(E);
+    *tr_out = tr;
+}
+
+// Gauss-Newton polish of one solution of the five-point problem in null-space coordinates c (E = sum_k c[k] L[.][k],
+// |c| = 1): the ten cubic constraints are evaluated on E itself, so the result does not inherit the conditioning of
+// the elimination that produced the start value.  OpenCV does not polish, but on well-conditioned samples its roots
+// are accurate to ~1e-12 and the polished solutions reproduce its inlier counts (tools/ransac_agreement.py);
+// un-polished roots of an ill-conditioned elimination were off by up to 0.2 in E.  Keeps the start value unless
+// the residual shrinks.
+VS_HD inline double polish_residual(const double L[9][4], const double* c, double* E, double* f, double* EEt, double* tr)
+{
+    for (int e = 0; e < 9; ++e) E[e] = c[0] * L[e][0] + c[1] * L[e][1] + c[2] * L[e][2] + c[3] * L[e][3];
+    e_constraints(E, f, EEt, tr);
+    f[10] = c[0] * c[0] + c[1] * c[1] + c[2] * c[2] + c[3] * c[3] - 1.0;
+    double r2 = 0.0;
+    for (int i = 0; i < 11; ++i) r2 += f[i] * f[i];
+    return r2;
+}
+
+// Returns the final squared residual; *start_r2 receives the residual of the start value.
+// NOT inlined on the device, on purpose: with this function inlined into the loop over the roots, cicc 12.9 (-O1 and
+// above; -Xcicc -O0, -G and g++ are fine, ASan/UBSan find nothing) produced code in which entries 1.. of the caller's
+// root list read back as 0 after the first polish -- its local arrays were overlaid on the live list.  Repro and
+// device-vs-host check of the solver: tools/ubench/solve5_device.cu.
+VS_HD VS_NOINLINE double polish_5pt(const double L[9][4], double c[4], double* start_r2)
+{
+    double E[9], f[11], EEt[9], tr;
+    double r2 = polish_residual(L, c, E, f, EEt, &tr);
+    *start_r2 = r2;
+    for (int it = 0; it < 12 && r2 > 1e-30 && isfinite(r2); ++it) {
+#ifdef VS_POLISH_TRACE
+        VS_POLISH_TRACE(it, r2, c);
+#endif
+        // cofactors of E (d det = sum cof_ij D_ij)
+        const double cof[9] = {E[4] * E[8] - E[5] * E[7], E[5] * E[6] - E[3] * E[8], E[3] * E[7] - E[4] * E[6],
+                               E[2] * E[7] - E[1] * E[8], E[0] * E[8] - E[2] * E[6], E[1] * E[6] - E[0] * E[7],
+                               E[1] * E[5] - E[2] * E[4], E[2] * E[3] - E[0] * E[5], E[0] * E[4] - E[1] * E[3]};
+        double J[11][4];
+        for (int k = 0; k < 4; ++k) {
+            double D[9], G[9];                                    // direction and D E^T
+            for (int e = 0; e < 9; ++e) D[e] = L[e][k];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j)
+                    G[3 * i + j] = D[3 * i] * E[3 * j] + D[3 * i + 1] * E[3 * j + 1] + D[3 * i + 2] * E[3 * j + 2];
+            const double dtr = 2.0 * (G[0] + G[4] + G[8]);
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) {
+                    double v = 0.0;
+                    for (int m = 0; m < 3; ++m)
+                        v += (G[3 * i + m] + G[3 * m + i]) * E[3 * m + j] + EEt[3 * i + m] * D[3 * m + j];
+                    J[3 * i + j][k] = 2.0 * v - dtr * E[3 * i + j] - tr * D[3 * i + j];
+                }
+            double dd = 0.0;
+            for (int e = 0; e < 9; ++e) dd += cof[e] * D[e];
+            J[9][k] = dd;
+            J[10][k] = 2.0 * c[k];
+        }
+        // normal equations (4 x 4): Gaussian elimination with pivoting
+        double N[4][5];
+        for (int a = 0; a < 4; ++a) {
+            for (int b = 0; b < 4; ++b) {
+                double v = 0.0;
+                for (int i = 0; i < 11; ++i) v += J[i][a] * J[i][b];
+                N[a][b] = v;
+            }
+            double g = 0.0;
+            for (int i = 0; i < 11; ++i) g += J[i][a] * f[i];
+            N[a][4] = -g;
+        }
+        bool ok = true;
+        for (int a = 0; a < 4 && ok; ++a) {
+            int pr = a;
+            for (int r = a + 1; r < 4; ++r)
+                if (fabs(N[r][a]) > fabs(N[pr][a])) pr = r;
+            if (!(fabs(N[pr][a]) > 1e-300)) { ok = false; break; }
+            if (pr != a)
+                for (int b = 0; b < 5; ++b) { const double t = N[a][b]; N[a][b] = N[pr][b]; N[pr][b] = t; }
+            const double inv = 1.0 / N[a][a];
+            for (int r = 0; r < 4; ++r) {
+                if (r == a) continue;
+                const double m = N[r][a] * inv;
+                for (int b = a; b < 5; ++b) N[r][b] -= m * N[a][b];
+            }
+        }
+        if (!ok) break;
+        double d[4], step2 = 0.0;
+        for (int k = 0; k < 4; ++k) { d[k] = N[k][4] / N[k][k]; step2 += d[k] * d[k]; }
+        if (!isfinite(step2)) break;
+        // backtracking: halve the step until the residual does not grow
+        double cn[4], rn = 0.0, lam = 1.0;
+        bool moved = false;
+        for (int h = 0; h < 8; ++h, lam *= 0.5) {
+            for (int k = 0; k < 4; ++k) cn[k] = c[k] + lam * d[k];
+            rn = polish_residual(L, cn, E, f, EEt, &tr);
+            if (rn < r2) { moved = true; break; }
+        }
+        if (!moved) { polish_residual(L, c, E, f, EEt, &tr); break; }
+        for (int k = 0; k < 4; ++k) c[k] = cn[k];
+        r2 = rn;
+        if (step2 * lam * lam < 1e-28) break;
     }
-    null_space_9<5>(A, nb);
+    return r2;
+}
+
+// One pass of Nister's elimination in the null-space basis nb (orthonormal rows): appends the polished real solutions
+// that are not yet in E[0..n) and returns the new count.  *trouble is set when the pass cannot be trusted to be
+// complete: a root of the degree-10 polynomial started far from a solution (the elimination lost digits), two roots
+// polished into one solution (so another one was probably missed), or a polish did not converge.
+VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int n, bool* trouble)
+{
+    const int have_before = n;
     // entry e = 3*i + j of E as a linear form in (x, y, z, 1)
     double L[9][4];
     for (int e = 0; e < 9; ++e)
@@ -235,10 +360,17 @@ VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double 
         for (int i = 0; i <= 10; ++i) det[i] += prod[i];
     }
     double zs[10];
-    const int nz = real_roots_deg10(det, zs);
-    int n = 0;
+    bool deflated = false;
+    const int nz = real_roots_deg10(det, zs, &deflated);
+    if (deflated) *trouble = true;
+#ifdef VS_5PT_TRACE
+    VS_5PT_TRACE(det, zs, nz);
+#endif
     for (int s = 0; s < nz; ++s) {
         const double z = zs[s];
+#ifdef VS_5PT_TRACE2
+        VS_5PT_TRACE2(s, nz, z);
+#endif
         double b[3][3];
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) {
@@ -258,15 +390,68 @@ VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double 
             }
         }
         if (bestD == 0.0 || !isfinite(x) || !isfinite(y)) continue;
-        double nrm = 0.0;
+        double cc[4] = {x, y, z, 1.0};
+        {
+            const double cn = 1.0 / sqrt(x * x + y * y + z * z + 1.0);
+            for (int k = 0; k < 4; ++k) cc[k] *= cn;
+        }
+        double r_start;
+        const double r_end = polish_5pt(L, cc, &r_start);
+        if (!(r_start < 1e-12)) *trouble = true;
+        if (!(r_end < 1e-16)) { *trouble = true; continue; }       // not a solution of the constraints
+        double Ek[9], nrm = 0.0;
         for (int e = 0; e < 9; ++e) {
-            E[n][e] = x * L[e][0] + y * L[e][1] + z * L[e][2] + L[e][3];
-            nrm += E[n][e] * E[n][e];
+            Ek[e] = cc[0] * L[e][0] + cc[1] * L[e][1] + cc[2] * L[e][2] + cc[3] * L[e][3];
+            nrm += Ek[e] * Ek[e];
         }
         if (!(nrm > 0.0) || !isfinite(nrm)) continue;
         nrm = 1.0 / sqrt(nrm);               // Frobenius norm 1 => singular values (1/sqrt2, 1/sqrt2, 0), as cv2 returns
-        for (int e = 0; e < 9; ++e) E[n][e] *= nrm;
+        bool dup = false;
+        for (int j = 0; j < n && !dup; ++j) {
+            double dp = 0.0, dm = 0.0;
+            for (int e = 0; e < 9; ++e) {
+                dp = fmax(dp, fabs(E[j][e] - Ek[e] * nrm));
+                dm = fmax(dm, fabs(E[j][e] + Ek[e] * nrm));
+            }
+            dup = fmin(dp, dm) < 1e-7;
+        }
+        if (dup) { if (have_before <= 0) *trouble = true; continue; }
+        if (n >= 10) break;
+        for (int e = 0; e < 9; ++e) E[n][e] = Ek[e] * nrm;
         ++n;
+    }
+    return n;
+}
+
+// 5-point solver.  x1, x2: 5 correspondences in normalised camera coordinates.
+// Writes up to 10 essential matrices (row-major, x2^T E x1 = 0, Frobenius norm 1); returns the count.
+// The roots are those of the five-point problem itself (every solution is polished on the cubic constraints), not of
+// one particular elimination: when the first pass reports trouble -- the z-coordinates of several solutions cluster in
+// this basis and the degree-10 polynomial is ill-conditioned -- a second pass in a rotated basis (a fixed orthogonal
+// 4 x 4 mix, so other coordinates play the role of z) contributes the solutions the first one missed.
+VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double E[10][9])
+{
+    double A[5][9], nb[4][9];
+    for (int i = 0; i < 5; ++i) {
+        const double u = x1[i][0], v = x1[i][1], up = x2[i][0], vp = x2[i][1];
+        A[i][0] = up * u; A[i][1] = up * v; A[i][2] = up;
+        A[i][3] = vp * u; A[i][4] = vp * v; A[i][5] = vp;
+        A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
+    }
+    null_space_9<5>(A, nb);
+    bool trouble = false;
+    int n = solve_5pt_in_basis(nb, E, 0, &trouble);
+    if (trouble) {
+        double rb[4][9];
+        for (int e = 0; e < 9; ++e) {
+            const double a = nb[0][e], b = nb[1][e], c = nb[2][e], d = nb[3][e];
+            rb[0][e] = 0.5 * (a + b + c + d);
+            rb[1][e] = 0.5 * (a - b + c - d);
+            rb[2][e] = 0.5 * (a + b - c - d);
+            rb[3][e] = 0.5 * (a - b - c + d);
+        }
+        bool t2 = false;
+        n = solve_5pt_in_basis(rb, E, n, &t2);
     }
     return n;
 }

@@ -11,8 +11,10 @@
 
 #ifdef __CUDACC__
 #define VS_HD __host__ __device__
+#define VS_NOINLINE __noinline__ inline
 #else
 #define VS_HD
+#define VS_NOINLINE inline
 #endif
 
 // Null space of an R x 9 matrix (R < 9) of full row rank: reduce to RREF with full
@@ -60,6 +62,21 @@ VS_HD inline void null_space_9(double A[R][9], double basis[9 - R][9])
         nrm = 1.0 / sqrt(nrm);
         for (int j = 0; j < 9; ++j) basis[k][colperm[j]] = v[j] * nrm;
     }
+    // orthonormal basis (modified Gram-Schmidt, two passes): the RREF vectors can be nearly parallel, and the
+    // polynomial systems built on the basis (the 5-point elimination above all) lose digits with its conditioning;
+    // OpenCV takes the basis from an SVD, i.e. orthonormal.
+    for (int pass = 0; pass < 2; ++pass)
+        for (int k = 0; k < 9 - R; ++k) {
+            for (int p = 0; p < k; ++p) {
+                double d = 0.0;
+                for (int j = 0; j < 9; ++j) d += basis[k][j] * basis[p][j];
+                for (int j = 0; j < 9; ++j) basis[k][j] -= d * basis[p][j];
+            }
+            double nrm = 0.0;
+            for (int j = 0; j < 9; ++j) nrm += basis[k][j] * basis[k][j];
+            nrm = nrm > 0.0 ? 1.0 / sqrt(nrm) : 0.0;
+            for (int j = 0; j < 9; ++j) basis[k][j] *= nrm;
+        }
 }
 
 VS_HD inline double det3(const double* m)

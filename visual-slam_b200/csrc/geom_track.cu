@@ -19,6 +19,7 @@
 //      solver and error function as vslam_ransac_essential_host, so a batch entry equals the host call;
 //   E  recoverPose: decomposeEssentialMat by one thread, cheirality of the four candidates per point.
 #include <float.h>
+#include <limits.h>
 #include <math.h>
 
 #include "common.cuh"
@@ -53,7 +54,9 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
                         double* __restrict__ out_t, int32_t* __restrict__ out_status)
 {
     __shared__ double s_models[TK_R * 10 * 9];
-    __shared__ int s_nm[TK_R], s_counts[TK_R * 10];
+    __shared__ int s_nm[TK_R], s_counts[TK_R * 10], s_idx[TK_R * 5];
+    __shared__ unsigned long long s_rng_cursor;
+    __shared__ int s_fail;
     __shared__ double s_best[9], s_R1[9], s_R2[9], s_t[3];
     __shared__ Proj s_cand[4];
     __shared__ int s_cursor[258], s_warp[TK_THREADS / 32];
@@ -154,7 +157,8 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
         p1[i] = make_double2(((double)a.x - P.cx) / P.fx, ((double)a.y - P.cy) / P.fy);
         p2[i] = make_double2(((double)b.x - P.cx) / P.fx, ((double)b.y - P.cy) / P.fy);
     }
-    if (tid == 0) { s_niters = P.max_iters; s_maxgood = 0; }
+    if (tid == 0) { s_niters = P.max_iters; s_maxgood = 0; s_rng_cursor = 0ull; s_fail = INT_MAX; }
+    const uint32_t salt = vs_seed_salt(P.seed);
     __syncthreads();
 
     // ---- D. RANSAC rounds
@@ -162,12 +166,14 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
     // sample: packed into one warp it costs one instruction stream per round instead of one per warp; the other
     // warps wait at the barrier and the SM's other CTAs fill the issue slots).
     for (int r0 = 0, R = TK_R0; r0 < s_niters; r0 += R, R = TK_R) {
+        // the round's subsets from OpenCV's stream (EMEstimatorCallback has no checkSubset), drawn by warp 0
+        if (wid == 0) cv_sample_round<5, false>(&s_rng_cursor, salt, n2, r0, R, s_idx, &s_fail, nullptr, nullptr, 10000);
+        __syncthreads();
         if (tid < R) {
             const int j = tid, it = r0 + j;
             int ne = 0;
-            if (it < P.max_iters) {
-                int idx[5];
-                draw_sample<5>(P.seed, it, n2, idx);
+            if (it < P.max_iters && it < s_fail) {
+                const int* idx = s_idx + j * 5;
                 double x1[5][2], x2[5][2];
                 for (int k = 0; k < 5; ++k) {
                     const double2 a = p1[idx[k]], b = p2[idx[k]];
@@ -194,7 +200,7 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
         }
         __syncthreads();
         if (tid == 0) {       // cv::RANSACPointSetRegistrator::run over this round, model_points = 5
-            int niters = s_niters, max_good = s_maxgood;
+            int niters = min(s_niters, s_fail), max_good = s_maxgood;
             for (int j = 0; j < R && r0 + j < niters; ++j)
                 for (int k = 0; k < s_nm[j]; ++k) {
                     const int good = s_counts[j * 10 + k];

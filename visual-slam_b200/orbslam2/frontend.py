@@ -106,7 +106,7 @@ def track_pair(pts1, descriptors1, pts2, descriptors2, camera_matrix, image_shap
 
 
 # --------------------------------------------------------------------------- full front end, batched
-def front_end_full(handle, frames, ratio=0.75, threshold=3.0, confidence=0.99, max_iters=1000, seed=0x5EED):
+def front_end_full(handle, frames, ratio=0.75, threshold=3.0, confidence=0.99, max_iters=1000, seed=0):
     """BASELINE config 3 ("full front-end"): extract every frame, match frame i with i+1, and filter every
     match list with the fundamental-matrix RANSAC (matcher.py:171-200) -- all on the device, one host
     round trip.  `handle` is an `_native.OrbHandle`, `frames` uint8 [B, H, W].
@@ -315,8 +315,10 @@ class _Cv2Proxy:
         if method is None:
             method = cv2.FM_RANSAC
         n = len(points1)
-        if method != cv2.FM_RANSAC or mask is not None or n < 8:
-            return cv2.findFundamentalMat(points1, points2, method, ransacReprojThreshold, confidence, maxIters)
+        if method != cv2.FM_RANSAC or n < 8:
+            # no CPU fallback in this package: the reference's callers use FM_RANSAC on >= 8 matches only
+            # (local_mapper.py:136 after its own len check, matcher.py:184-192)
+            raise NotImplementedError("findFundamentalMat on the B200 kernels: FM_RANSAC with at least 8 points only")
         from .utils import find_fundamental_ransac
         return find_fundamental_ransac(np.asarray(points1, np.float32).reshape(-1, 2),
                                        np.asarray(points2, np.float32).reshape(-1, 2),

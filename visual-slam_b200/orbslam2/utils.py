@@ -12,7 +12,9 @@ import numpy as np
 from . import _native
 
 RANSAC = 8          # value of cv2.RANSAC, so that callers can pass method=cv2.RANSAC unchanged
-DEFAULT_SEED = 0x5EED
+# seed 0 = OpenCV's own sample stream (cv::RNG(-1) on every call; the reference cannot change it: cv2's estimators
+# ignore cv2.setRNGSeed).  Any other value gives a different deterministic stream.
+DEFAULT_SEED = 0
 
 
 def _pts(p):
@@ -30,7 +32,7 @@ def find_fundamental_ransac(points1, points2, threshold=3.0, confidence=0.99, ma
     _native.check(_native.lib().vslam_ransac_fundamental_host(_native.ptr(p1), _native.ptr(p2), n, float(threshold),
                                                               float(confidence), int(max_iters), C.c_uint64(seed),
                                                               _native.ptr(F), _native.ptr(mask), C.byref(cnt)))
-    if cnt.value == 0:
+    if not F.any():                  # no model (cv2 returns None); the LMedS path (n < 15) still reports its mask
         return None, mask.reshape(-1, 1)
     return F.reshape(3, 3), mask.reshape(-1, 1)
 
