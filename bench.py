@@ -210,11 +210,126 @@ def run_reference_arm(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload), "frames_per_step": per_step},
+            "config": config_block(args.workload, args.batch or WORKLOADS[args.workload][3], max(args.gpus, 1), args.steps),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
-                             "sample": "%d frames per step; %s" % (per_step, sample)},
+                             "sample": "bounded sample: %d frames of the workload per step (the GPU arm's step is the full "
+                                       "batch); %s" % (per_step, sample)},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def config_block(workload, B, world, K):
+    """The `config` object of both arms (the reference arm times a bounded sample of the same workload)."""
+    w, h, _, _ = WORKLOADS[workload]
+    return {"workload": workload_name(workload), "frames_per_step_per_gpu": B,
+            "l2_policy": "inputs larger than L2 (%.0f MB of frames per step)" % (B * w * h / 1e6),
+            "sharding": "one clip of world x B x steps frames, contiguous range per rank (sharding.frame_range), "
+                        "1 boundary descriptor block per rank boundary"}
+
+
+def matching_block(pairs_per_s, ms_per_step):
+    """kNN-2 = binary GEMM on tcgen05 kind::i8 (256 u8 MACs per descriptor pair).  Two denominators: the nominal
+    dense int8 tensor rate (B200_PROFILING.md, 4.5 Pop/s; MEASURED_PEAKS.json holds no integer-MMA peak) and the
+    MEASURED POPC-pipe rate of tools/ubench/popc.cu (profiles/r2_popc_peak.json) -- the roofline of the XOR + POPC
+    formulation north_star names, which the tensor-core kernel is measured against as a multiple."""
+    blk = {"ms_per_step": ms_per_step, "gpairs_per_s": pairs_per_s / 1e9,
+           "engine": os.environ.get("VSLAM_KNN", "tcgen05"),
+           "tensor_pops": pairs_per_s * 512.0 / 1e15, "tensor_peak_pops": 4.5,
+           "tensor_frac": pairs_per_s * 512.0 / 4.5e15}
+    try:
+        pk = json.load(open(os.path.join(ROOT, "profiles", "r2_popc_peak.json")))
+        peak = float(pk["pairs256_per_s_at_8_popc"])
+        blk["popc_pipe_peak_gpairs_per_s"] = peak / 1e9
+        blk["vs_popc_pipe_peak"] = pairs_per_s / peak
+        blk["popc_peak_source"] = "profiles/r2_popc_peak.json (tools/ubench/popc.cu, measured on this pool's B200)"
+    except Exception:
+        pass
+    return blk
+
+
+def _kp_table(kps):
+    return np.array([(k.pt[0], k.pt[1], k.octave) for k in kps], np.float64).reshape(-1, 3)
+
+
+def parity_gates(f0, f1, n_features, out, cap):
+    """BASELINE.md section 4 gates on the first frame pair of the step, against cv2 itself (the reference's calls):
+    kp_agree = fraction of cv2's keypoints with one of ours at the same octave within 0.5 px, desc_identical =
+    fraction of those whose 32 descriptor bytes are equal, match_lists_equal = cv2's ratio-test match list on its own
+    descriptors equals ours as a set of (pt1, pt2, distance).  `out` = the pinned results of the e2e call."""
+    try:
+        import cv2
+    except ImportError:
+        return {"unavailable": "cv2 is not importable on this box"}
+    orb = cv2.ORB_create(nfeatures=n_features, scaleFactor=SCALE, nlevels=N_LEVELS, edgeThreshold=31, firstLevel=0,
+                         WTA_K=2, scoreType=cv2.ORB_HARRIS_SCORE, patchSize=31, fastThreshold=FAST_THR)
+    res = {"against": "cv2 %s on frames 0 and 1 of the shard" % cv2.__version__}
+    kp_np, desc_np, cnt_np, match_np, mcnt_np = [x.numpy() for x in out]
+    agree, ident, total = 0, 0, 0
+    ref_desc, ref_kp = [], []
+    for f, img in enumerate((f0, f1)):
+        kps, desc = orb.detectAndCompute(img, None)
+        ref_kp.append(kps)
+        ref_desc.append(desc)
+        n = int(cnt_np[f])
+        mine = {}
+        for i in range(min(n, cap)):
+            x, y, octave = float(kp_np[f, i, 0]), float(kp_np[f, i, 1]), int(kp_np[f, i, 5:6].view(np.int32)[0])
+            mine[(round(x * 4), round(y * 4), octave)] = i
+        for j, k in enumerate(kps):
+            total += 1
+            i = mine.get((round(k.pt[0] * 4), round(k.pt[1] * 4), k.octave))
+            if i is not None and abs(kp_np[f, i, 0] - k.pt[0]) <= 0.5 and abs(kp_np[f, i, 1] - k.pt[1]) <= 0.5:
+                agree += 1
+                ident += bool(np.array_equal(desc_np[f, i], desc[j]))
+    res["kp_agree"] = agree / max(total, 1)
+    res["desc_identical"] = ident / max(agree, 1)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)
+    ref = set()
+    for pair in bf.knnMatch(ref_desc[0], ref_desc[1], k=2):
+        if len(pair) >= 2 and pair[0].distance < RATIO * pair[1].distance or len(pair) == 1:
+            m = pair[0]
+            ref.add((ref_kp[0][m.queryIdx].pt, ref_kp[1][m.trainIdx].pt, ref_kp[0][m.queryIdx].octave, float(m.distance)))
+    got = set()
+    for q, t, d in match_np[0][:int(mcnt_np[0])]:
+        got.add(((float(kp_np[0, q, 0]), float(kp_np[0, q, 1])), (float(kp_np[1, t, 0]), float(kp_np[1, t, 1])),
+                 int(kp_np[0, q, 5:6].view(np.int32)[0]), float(d)))
+    res["match_lists_equal"] = ref == got
+    res["match_symmetric_difference"] = len(ref ^ got)
+    res["matches"] = len(got)
+    return res
+
+
+def cpu_baseline_block(w, h, n_features, frames):
+    """cpu_baseline of the bench line: the reference's calls on all host cores (the headline figure), plus a
+    1-thread column and per-stage milliseconds on a short sample."""
+    fps, cores, kind, sample = cpu_front_end_fps(w, h, n_features, frames)
+    blk = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}
+    try:
+        import cv2
+        orb = cv2.ORB_create(nfeatures=n_features, scaleFactor=SCALE, nlevels=N_LEVELS, edgeThreshold=31, firstLevel=0,
+                             WTA_K=2, scoreType=cv2.ORB_HARRIS_SCORE, patchSize=31, fastThreshold=FAST_THR)
+        bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=False)
+        for threads, key in ((cores, "all_threads"), (1, "one_thread")):
+            cv2.setNumThreads(threads)
+            n = 6 if w <= 640 else 3
+            te = tm = 0.0
+            prev = None
+            for f in frames[:n + 1]:
+                t0 = time.perf_counter()
+                _, d = orb.detectAndCompute(f, None)
+                t1 = time.perf_counter()
+                if prev is not None:
+                    pairs = bf.knnMatch(prev, d, k=2)
+                    _ = [p[0] for p in pairs if len(p) >= 2 and p[0].distance < RATIO * p[1].distance]
+                    tm += time.perf_counter() - t1
+                    te += t1 - t0
+                prev = d
+            blk[key] = {"threads": threads, "extract_ms_per_frame": 1e3 * te / n, "match_ms_per_pair": 1e3 * tm / n,
+                        "frames_per_s": n / (te + tm)}
+        cv2.setNumThreads(cores)
+    except ImportError:
+        pass
+    return blk
 
 
 def workload_name(key):
@@ -241,7 +356,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="frames per step per GPU (0 = workload default)")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg and the cv2 parity gates")
+    ap.add_argument("--no-affinity", action="store_true", help="do not bind the rank to the CPUs near its GPU")
+    ap.add_argument("--latency", action="store_true",
+                    help="latency mode: p50 / p99 of the per-frame calls the reference's callers make (C2, 1 GPU)")
     ap.add_argument("--distribution", default="cv2", choices=["cv2", "orbslam2"],
                     help="keypoint distribution: cv2 = the reference's cv2.ORB retain-best (the metric's config), "
                          "orbslam2 = ini/min cell thresholds + quadtree (SURVEY 8(f) N4)")
@@ -264,6 +382,10 @@ def main():
         sys.exit(2)
     B = args.batch or WORKLOADS[args.workload][3]
     sys.modules.setdefault("bench", sys.modules[__name__])
+    if args.latency:
+        from bench_latency import run_latency
+        run_latency(args)
+        return
     from bench_gpu_arm import run_gpu_arm
     run_gpu_arm(args, rank, world, B)
 

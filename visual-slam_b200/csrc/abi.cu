@@ -216,6 +216,7 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_ext[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_done[i], cudaEventDisableTiming);
     }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&o->ev_host_done, cudaEventDisableTiming | cudaEventBlockingSync);
     if (e != cudaSuccess) { vslam_orb_destroy(o); return vs_cuda_fail(e, "orb_create init", __FILE__, __LINE__); }
     *out = o;
     return VSLAM_OK;
@@ -237,6 +238,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
         if (o->ev_ext[i]) cudaEventDestroy(o->ev_ext[i]);
         if (o->ev_done[i]) cudaEventDestroy(o->ev_done[i]);
     }
+    if (o->ev_host_done) cudaEventDestroy(o->ev_host_done);
     for (cudaEvent_t e : o->prof_ev) if (e) cudaEventDestroy(e);
     delete o;
     return VSLAM_OK;
@@ -281,6 +283,15 @@ extern "C" int vslam_orb_detect_and_compute(vslam_orb* o, const uint8_t* d_frame
     VS_REQUIRE(o && d_frames && d_kp && d_desc && d_count, "null argument");
     VS_REQUIRE(batch >= 1 && batch <= o->prm.max_batch, "batch exceeds max_batch");
     VS_REQUIRE(pitch >= o->prm.width, "pitch smaller than width");
+    {   // the handle's workspace, streams and kernel attributes belong to the device it was created on
+        int dev = -1;
+        VS_CUDA(cudaGetDevice(&dev));
+        if (dev != o->device) {
+            vs_set_error("vslam_orb_detect_and_compute: handle was created on device %d, current device is %d "
+                         "(cudaSetDevice first; one handle per device)", o->device, dev);
+            return VSLAM_E_INVALID;
+        }
+    }
     cudaStream_t s = (cudaStream_t)stream;
     o->last_stream = s;
     o->last_frames = d_frames;

@@ -384,19 +384,21 @@ vs_knn2_tc5_kernel(const uint8_t* __restrict__ query, int nq_max, long q_stride,
 
 #define T5_DYN_SMEM (2 * T5_OPER_BYTES + T5_STAGES * T5_TILE_BYTES + 128)
 
+// function attributes and memory pools belong to a device (context), not to the process: configure each device once
 int vs_knn2_tc5_configure()
 {
-    static int done = 0;
-    if (!done) {
+    static unsigned long long done_mask = 0;       // bit per device ordinal
+    int dev = 0;
+    VS_CUDA(cudaGetDevice(&dev));
+    const unsigned long long bit = dev >= 0 && dev < 64 ? 1ull << dev : 0ull;
+    if (!bit || !(__atomic_load_n(&done_mask, __ATOMIC_ACQUIRE) & bit)) {
         VS_CUDA(cudaFuncSetAttribute(vs_knn2_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T5_DYN_SMEM));
         // the expanded train tiles live in stream-ordered allocations: keep freed blocks in the pool
         cudaMemPool_t pool;
-        int dev = 0;
-        VS_CUDA(cudaGetDevice(&dev));
         VS_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
         unsigned long long keep = ~0ull;
         VS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-        done = 1;
+        __atomic_fetch_or(&done_mask, bit, __ATOMIC_RELEASE);
     }
     return VSLAM_OK;
 }

@@ -109,6 +109,7 @@ struct vslam_orb {
     // chunked host pipeline (vslam_frontend_run_host): copy-in / copy-out streams and per-chunk events
     cudaStream_t stream_in, stream_out, stream2;   // stream / stream2 alternate between compute chunks
     cudaEvent_t ev_in[VS_HOST_CHUNKS], ev_ext[VS_HOST_CHUNKS], ev_done[VS_HOST_CHUNKS];
+    cudaEvent_t ev_host_done;  // blocking-sync event: end of a *_host call (the waiting host thread sleeps instead of spinning)
     int knn_no_split;          // set on the per-chunk views: the split-train scratch of kNN-2 is not per stream
     cudaStream_t last_stream;
     const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)

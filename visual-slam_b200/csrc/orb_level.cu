@@ -615,7 +615,15 @@ int vs_configure_level_smem(const VsPlan& p)
         vs_set_error("scale_factor too large for the level kernel's parent staging (%zu bytes)", dyn);
         return VSLAM_E_INVALID;
     }
-    VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    // only ever raised, per device: handles with different plans (scale factors) share the function attribute
+    static int cur[64] = {};
+    int dev = 0;
+    VS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) dev = 0;
+    if ((int)dyn > __atomic_load_n(&cur[dev], __ATOMIC_ACQUIRE)) {
+        VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        __atomic_store_n(&cur[dev], (int)dyn, __ATOMIC_RELEASE);
+    }
     return VSLAM_OK;
 }
 

@@ -689,10 +689,17 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
     }
 }
 
+// The attribute belongs to (function, device): it is only ever raised, per device, so that a second handle with a
+// smaller plan cannot pull it below what an older handle's launches need.
 void vs_configure_select_smem(int bytes)
 {
-    if (bytes > 48 * 1024)
-        cudaFuncSetAttribute(vs_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    static int cur[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (bytes > 48 * 1024 && bytes > __atomic_load_n(&cur[dev], __ATOMIC_ACQUIRE)) {
+        if (cudaFuncSetAttribute(vs_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) == cudaSuccess)
+            __atomic_store_n(&cur[dev], bytes, __ATOMIC_RELEASE);
+    }
 }
 
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
