@@ -137,6 +137,15 @@ int vslam_orb_compute_host(vslam_orb* orb, const uint8_t* h_frame, const float* 
                            const float* h_y, const float* h_angle, const int32_t* h_octave,
                            int n, uint8_t* h_desc, int32_t* h_keep_index, int* n_out);
 
+/* The same on device buffers: the pyramid of d_frame (uint8 [height][pitch]) is built in the
+ * handle's workspace, then row i of d_desc (uint8 [n][32]) is the descriptor of keypoint i of the device arrays
+ * d_x / d_y / d_angle (float [n]) / d_octave (int32 [n]), in the caller's order.  d_keep_mask uint8 [n] (may be
+ * NULL): 1 where the keypoint passes cv2's border test and its octave is a planned level, else 0 and the row is
+ * zero -- the host form above does the compaction and level-major ordering on top of this.  Enqueues only. */
+int vslam_orb_compute(vslam_orb* orb, const uint8_t* d_frame, int pitch, const float* d_x, const float* d_y,
+                      const float* d_angle, const int32_t* d_octave, int n, uint8_t* d_desc,
+                      uint8_t* d_keep_mask, void* stream);
+
 /* Replaces cv2.cvtColor(image, COLOR_BGR2GRAY) at extractor.py:62,81,101. */
 int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_gray);
 
@@ -148,6 +157,14 @@ int vslam_bgr2gray_host(const uint8_t* h_bgr, int height, int width, uint8_t* h_
 int vslam_gftt_grid_host(const uint8_t* h_frame, int height, int width, int rows, int cols,
                          int max_per_cell, double quality, double min_distance,
                          float* h_xy, int32_t* h_cell_count, int* n_out);
+
+/* The same on a device frame (uint8 [height][width], tightly packed): d_xy float [rows*cols][max_per_cell][2]
+ * holds cell c's corners in acceptance order at row c (not compacted), d_cell_count int32 [rows*cols]; d_status
+ * (1 int32, may be NULL) becomes non-zero when a cell held more local maxima than the candidate staging.  The
+ * min-eigenvalue maps live in per-thread scratch of the library.  Enqueues only. */
+int vslam_gftt_grid(const uint8_t* d_frame, int height, int width, int rows, int cols, int max_per_cell,
+                    double quality, double min_distance, float* d_xy, int32_t* d_cell_count, int32_t* d_status,
+                    void* stream);
 
 /* Per-kernel timing for bench.py's roofline figures: when enabled, CUDA events are
  * recorded on the launching stream between the kernels of every call on this handle.
@@ -243,6 +260,12 @@ int vslam_score_fundamental_host(const double* h_F, const float* h_p1, const flo
 int vslam_score_essential_host(const double* h_E, const double* h_K, const float* h_p1,
                                const float* h_p2, int n, double thr, uint8_t* h_mask,
                                int* n_inliers);
+/* Device-pointer forms of the two scoring calls (points float [n][2] on the device, mask uint8 [n] on the device or
+ * NULL; the models are host pointers).  n_inliers (host, may be NULL) makes the call wait for the stream. */
+int vslam_score_fundamental(const double* h_F, const float* d_p1, const float* d_p2, int n, double thr,
+                            uint8_t* d_mask, int* n_inliers, void* stream);
+int vslam_score_essential(const double* h_E, const double* h_K, const float* d_p1, const float* d_p2, int n,
+                          double thr, uint8_t* d_mask, int* n_inliers, void* stream);
 /* Replaces cv2.findFundamentalMat(p1, p2, FM_RANSAC, thr, conf) (matcher.py:192):
  * 7-point hypotheses evaluated in parallel on the subsets OpenCV itself draws (its RNG(-1)
  * stream with duplicate and collinearity rejection), winner and stopping point by a replay of
@@ -276,11 +299,21 @@ int vslam_ransac_fundamental_batched(const vslam_keypoint* d_kp_query,
 int vslam_ransac_essential_host(const float* h_p1, const float* h_p2, int n, const double* h_K,
                                 double prob, double thr, int max_iters, uint64_t seed,
                                 double* h_E, uint8_t* h_mask, int* n_inliers);
+/* The same with the points and the mask on the device; E and the inlier count are host results, so
+ * the call waits for the stream.  (vslam_track_batched is the fully device-resident, batched form.) */
+int vslam_ransac_essential(const float* d_p1, const float* d_p2, int n, const double* h_K, double prob, double thr,
+                           int max_iters, uint64_t seed, double* h_E, uint8_t* d_mask, int* n_inliers,
+                           void* stream);
 /* Replaces cv2.recoverPose(E, p1, p2, K, mask) (utils.py:133, tracker.py:249).
  * h_mask_inout uint8 [n] (NULL = all ones on input, no output). */
 int vslam_recover_pose_host(const double* h_E, const float* h_p1, const float* h_p2, int n,
                             const double* h_K, uint8_t* h_mask_inout, double* h_R, double* h_t,
                             int* n_good);
+/* Device-pointer form: points float [n][2] and d_mask_inout uint8 [n] (may be NULL) on the device; R, t and the
+ * count are host results (the winner among the four candidates is picked on the host: the call waits for the
+ * stream once), the mask is updated on the stream. */
+int vslam_recover_pose(const double* h_E, const float* d_p1, const float* d_p2, int n, const double* h_K,
+                       uint8_t* d_mask_inout, double* h_R, double* h_t, int* n_good, void* stream);
 /* Batched, device-resident form of the reference's per-frame tracking step
  * (Tracker._track_frame, tracker.py:214-254) for the output of vslam_frontend_run: pair p
  * takes its match list d_match[p] (layout as above) through
@@ -323,6 +356,9 @@ int vslam_track_clip_host(vslam_orb* orb, const uint8_t* h_frames, int batch, do
  * h_X float [4][n] (row-major, un-normalised homogeneous, as cv2 returns it). */
 int vslam_triangulate_host(const double* h_P1, const double* h_P2, const float* h_p1,
                            const float* h_p2, int n, float* h_X);
+/* Device-pointer form: d_X float [4][n] on the device.  Enqueues only. */
+int vslam_triangulate(const double* h_P1, const double* h_P2, const float* d_p1, const float* d_p2, int n,
+                      float* d_X, void* stream);
 /* Replaces the per-point loop of LocalMapper._cull_map_points (local_mapper.py:205-237): a map
  * point is kept when it has at least min_observations observations and, walking them in stored
  * order, none has a reprojection error above max_error (5.0 in the reference):

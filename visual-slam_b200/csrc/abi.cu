@@ -36,6 +36,48 @@ extern "C" int vslam_device_count(void)
     return n;
 }
 
+// Per-thread, per-device scratch for the entry points that need a little device memory of their own (the *_host
+// wrappers, the device forms of the geometry calls): a few growing buffers per host thread instead of a
+// cudaMalloc / cudaFree pair per call.  Slots are independent buffers; a pointer stays valid until the same thread
+// asks the same slot for more.  Freed when the thread exits.
+namespace {
+struct TlsScratch {
+    void* p[VS_SCRATCH_SLOTS] = {};
+    size_t n[VS_SCRATCH_SLOTS] = {};
+    int dev = -1;
+    void release()
+    {
+        for (int i = 0; i < VS_SCRATCH_SLOTS; ++i) {
+            if (p[i]) cudaFree(p[i]);
+            p[i] = nullptr;
+            n[i] = 0;
+        }
+    }
+    ~TlsScratch() { release(); cudaGetLastError(); }
+};
+thread_local TlsScratch g_scratch;
+}
+
+int vs_scratch(int slot, size_t bytes, void** out)
+{
+    *out = nullptr;
+    VS_REQUIRE(slot >= 0 && slot < VS_SCRATCH_SLOTS, "bad scratch slot");
+    int dev = 0;
+    VS_CUDA(cudaGetDevice(&dev));
+    if (dev != g_scratch.dev) { g_scratch.release(); g_scratch.dev = dev; }
+    if (bytes < 256) bytes = 256;
+    if (bytes > g_scratch.n[slot]) {
+        if (g_scratch.p[slot]) { VS_CUDA(cudaDeviceSynchronize()); VS_CUDA(cudaFree(g_scratch.p[slot])); }
+        g_scratch.p[slot] = nullptr;
+        g_scratch.n[slot] = 0;
+        const size_t grow = bytes + bytes / 2;
+        VS_CUDA(cudaMalloc(&g_scratch.p[slot], grow));
+        g_scratch.n[slot] = grow;
+    }
+    *out = g_scratch.p[slot];
+    return VSLAM_OK;
+}
+
 static int check_device()
 {
     int dev = 0;

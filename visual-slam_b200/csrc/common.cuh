@@ -128,6 +128,10 @@ struct vslam_orb {
 #define VS_CTR_HIST 4
 #define VS_CTR_STRIDE (4 + 256)
 
+// per-thread, per-device scratch buffers (abi.cu): *out = device pointer of at least `bytes` bytes in `slot`
+#define VS_SCRATCH_SLOTS 8
+int vs_scratch(int slot, size_t bytes, void** out);
+
 // kernels / launchers implemented in the other translation units
 int vs_configure_level_smem(const VsPlan& p);
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s);

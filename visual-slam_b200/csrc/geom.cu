@@ -25,13 +25,6 @@
 
 namespace {
 
-struct DevMem {
-    void* p = nullptr;
-    ~DevMem() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
-    template <class T> T* as() { return (T*)p; }
-};
-
 // ---- scoring: one CTA per model -----------------------------------------------------------
 // mode 0: fundamental (float2 points), mode 1: essential (double2 normalised points)
 template <int MODE>
@@ -68,6 +61,37 @@ vs_score_models_kernel(const double* __restrict__ models, const int* __restrict_
     if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&s_cnt, cnt);
     __syncthreads();
     if (threadIdx.x == 0 && counts) counts[m] = s_cnt;
+}
+
+// scoring of ONE model (kernel argument) on float pixel coordinates; MODE 1 normalises by K in double first, as
+// cv::findEssentialMat does.  count (may be null) += inliers, one atomic per warp.
+struct Model9 { double m[9]; };
+struct Intr4 { double fx, fy, cx, cy; };
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+vs_score_points_kernel(Model9 M, Intr4 K, const float2* __restrict__ p1, const float2* __restrict__ p2, int n, float thr2,
+                       uint8_t* __restrict__ mask, int32_t* __restrict__ count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int in = 0;
+    if (i < n) {
+        const float2 a = p1[i], b = p2[i];
+        float err;
+        if (MODE == 0) err = f_error(M.m, a.x, a.y, b.x, b.y);
+        else err = e_error(M.m, ((double)a.x - K.cx) / K.fx, ((double)a.y - K.cy) / K.fy,
+                           ((double)b.x - K.cx) / K.fx, ((double)b.y - K.cy) / K.fy);
+        in = err <= thr2;
+        if (mask) mask[i] = (uint8_t)in;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, in);
+    if (count && (threadIdx.x & 31) == 0 && m) atomicAdd(count, __popc(m));
+}
+
+__global__ void vs_normalise_points_kernel(Intr4 K, const float2* __restrict__ p, int n, double2* __restrict__ q)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) q[i] = make_double2(((double)p[i].x - K.cx) / K.fx, ((double)p[i].y - K.cy) / K.fy);
 }
 
 // ---- hypotheses -------------------------------------------------------------------------
@@ -353,36 +377,65 @@ vs_ransac_f_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_
         if (e__ != cudaSuccess) return vs_cuda_fail(e__, #call, __FILE__, __LINE__);     \
     } while (0)
 
-static int score_common(int mode, const double* h_M, const void* d_p1, const void* d_p2, int n, float thr2,
-                        uint8_t* h_mask, int* n_inliers)
+// scoring of one model on device points: mask on the device, inlier count to the host when asked for (then the call
+// synchronises the stream)
+static int score_points(int mode, const double* h_M, const double* h_K, const float* d_p1, const float* d_p2, int n,
+                        float thr2, uint8_t* d_mask, int* n_inliers, cudaStream_t s)
 {
-    DevMem m, cnt, mask;
-    GEOM_CUDA(m.alloc(9 * sizeof(double)));
-    GEOM_CUDA(cnt.alloc(sizeof(int)));
-    GEOM_CUDA(mask.alloc(n));
-    GEOM_CUDA(cudaMemcpy(m.p, h_M, 9 * sizeof(double), cudaMemcpyHostToDevice));
+    if (n_inliers) *n_inliers = 0;
+    if (n == 0) return VSLAM_OK;
+    Model9 M;
+    memcpy(M.m, h_M, sizeof(M.m));
+    Intr4 K = {1, 1, 0, 0};
+    if (h_K) K = {h_K[0], h_K[4], h_K[2], h_K[5]};
+    void* cnt = nullptr;
+    if (n_inliers) {
+        int rc = vs_scratch(5, sizeof(int32_t), &cnt);
+        if (rc) return rc;
+        GEOM_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int32_t), s));
+    }
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (mode == 0)
-        vs_score_models_kernel<0><<<1, 128>>>(m.as<double>(), nullptr, 1, d_p1, d_p2, n, thr2, cnt.as<int>(), mask.as<uint8_t>());
+        vs_score_points_kernel<0><<<(n + 255) / 256, 256, 0, s>>>(M, K, (const float2*)d_p1, (const float2*)d_p2, n, thr2,
+                                                                 d_mask, (int32_t*)cnt);
     else
-        vs_score_models_kernel<1><<<1, 128>>>(m.as<double>(), nullptr, 1, d_p1, d_p2, n, thr2, cnt.as<int>(), mask.as<uint8_t>());
+        vs_score_points_kernel<1><<<(n + 255) / 256, 256, 0, s>>>(M, K, (const float2*)d_p1, (const float2*)d_p2, n, thr2,
+                                                                 d_mask, (int32_t*)cnt);
     GEOM_CUDA(cudaGetLastError());
-    int c = 0;
-    GEOM_CUDA(cudaMemcpy(&c, cnt.p, sizeof(int), cudaMemcpyDeviceToHost));
-    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, mask.p, n, cudaMemcpyDeviceToHost));
-    if (n_inliers) *n_inliers = c;
+    if (n_inliers) {
+        int32_t c = 0;
+        GEOM_CUDA(cudaMemcpyAsync(&c, cnt, sizeof(c), cudaMemcpyDeviceToHost, s));
+        GEOM_CUDA(cudaStreamSynchronize(s));
+        *n_inliers = c;
+    }
     return VSLAM_OK;
 }
 
-static void normalise_points(const float* p, int n, const double* K, std::vector<double>& out)
+extern "C" int vslam_score_fundamental(const double* h_F, const float* d_p1, const float* d_p2, int n, double thr,
+                                       uint8_t* d_mask, int* n_inliers, void* stream)
 {
-    // cv::findEssentialMat / recoverPose: double points, (x - cx) / fx, (y - cy) / fy
-    const double fx = K[0], fy = K[4], cx = K[2], cy = K[5];
-    out.resize((size_t)2 * n);
-    for (int i = 0; i < n; ++i) {
-        out[2 * i] = ((double)p[2 * i] - cx) / fx;
-        out[2 * i + 1] = ((double)p[2 * i + 1] - cy) / fy;
-    }
+    VS_REQUIRE(h_F && n >= 0 && (n == 0 || (d_p1 && d_p2)), "bad argument");
+    return score_points(0, h_F, nullptr, d_p1, d_p2, n, (float)(thr * thr), d_mask, n_inliers, (cudaStream_t)stream);
+}
+
+extern "C" int vslam_score_essential(const double* h_E, const double* h_K, const float* d_p1, const float* d_p2, int n,
+                                     double thr, uint8_t* d_mask, int* n_inliers, void* stream)
+{
+    VS_REQUIRE(h_E && h_K && n >= 0 && (n == 0 || (d_p1 && d_p2)), "bad argument");
+    VS_REQUIRE(h_K[0] != 0.0 && h_K[4] != 0.0, "singular camera matrix");
+    const double t = thr / ((h_K[0] + h_K[4]) / 2);
+    return score_points(1, h_E, h_K, d_p1, d_p2, n, (float)(t * t), d_mask, n_inliers, (cudaStream_t)stream);
+}
+
+// host points -> per-thread device scratch (slots 0, 1: points; 2: mask)
+static int stage_points(const float* h_p1, const float* h_p2, int n, void** a, void** b, void** m)
+{
+    int rc;
+    if ((rc = vs_scratch(0, (size_t)n * 8, a)) || (rc = vs_scratch(1, (size_t)n * 8, b)) || (rc = vs_scratch(2, (size_t)n, m)))
+        return rc;
+    GEOM_CUDA(cudaMemcpy(*a, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(*b, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    return VSLAM_OK;
 }
 
 extern "C" int vslam_score_fundamental_host(const double* h_F, const float* h_p1, const float* h_p2, int n,
@@ -391,12 +444,14 @@ extern "C" int vslam_score_fundamental_host(const double* h_F, const float* h_p1
     VS_REQUIRE(h_F && h_p1 && h_p2 && n >= 0, "bad argument");
     if (n_inliers) *n_inliers = 0;
     if (n == 0) return VSLAM_OK;
-    DevMem a, b;
-    GEOM_CUDA(a.alloc((size_t)n * 8));
-    GEOM_CUDA(b.alloc((size_t)n * 8));
-    GEOM_CUDA(cudaMemcpy(a.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemcpy(b.p, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
-    return score_common(0, h_F, a.p, b.p, n, (float)(thr * thr), h_mask, n_inliers);
+    void *a, *b, *m;
+    int rc = stage_points(h_p1, h_p2, n, &a, &b, &m);
+    if (rc) return rc;
+    int c = 0;
+    if ((rc = vslam_score_fundamental(h_F, (const float*)a, (const float*)b, n, thr, (uint8_t*)m, &c, nullptr))) return rc;
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, m, n, cudaMemcpyDeviceToHost));
+    if (n_inliers) *n_inliers = c;
+    return VSLAM_OK;
 }
 
 extern "C" int vslam_score_essential_host(const double* h_E, const double* h_K, const float* h_p1,
@@ -405,24 +460,31 @@ extern "C" int vslam_score_essential_host(const double* h_E, const double* h_K, 
     VS_REQUIRE(h_E && h_K && h_p1 && h_p2 && n >= 0, "bad argument");
     if (n_inliers) *n_inliers = 0;
     if (n == 0) return VSLAM_OK;
-    std::vector<double> q1, q2;
-    normalise_points(h_p1, n, h_K, q1);
-    normalise_points(h_p2, n, h_K, q2);
-    DevMem a, b;
-    GEOM_CUDA(a.alloc((size_t)n * 16));
-    GEOM_CUDA(b.alloc((size_t)n * 16));
-    GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
-    double t = thr / ((h_K[0] + h_K[4]) / 2);
-    return score_common(1, h_E, a.p, b.p, n, (float)(t * t), h_mask, n_inliers);
+    void *a, *b, *m;
+    int rc = stage_points(h_p1, h_p2, n, &a, &b, &m);
+    if (rc) return rc;
+    int c = 0;
+    if ((rc = vslam_score_essential(h_E, h_K, (const float*)a, (const float*)b, n, thr, (uint8_t*)m, &c, nullptr))) return rc;
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, m, n, cudaMemcpyDeviceToHost));
+    if (n_inliers) *n_inliers = c;
+    return VSLAM_OK;
 }
 
-// essential-matrix RANSAC: subsets from OpenCV's stream (host) -> hypotheses -> per-model counts -> sequential
-// replay of cv::RANSACPointSetRegistrator::run -> final mask
-static int ransac_e_driver(const void* d_p1, const void* d_p2, int n, float thr2, double conf, int max_iters,
-                           uint64_t seed, double* h_model, uint8_t* h_mask, int* n_inliers)
+// essential-matrix RANSAC on device points: subsets from OpenCV's stream (host) -> hypotheses -> per-model counts ->
+// sequential replay of cv::RANSACPointSetRegistrator::run -> final mask.  E and the inlier count are host results, so
+// the call synchronises the stream (twice: per-model counts, final count).
+extern "C" int vslam_ransac_essential(const float* d_p1, const float* d_p2, int n, const double* h_K, double prob,
+                                      double thr, int max_iters, uint64_t seed, double* h_E, uint8_t* d_mask,
+                                      int* n_inliers, void* stream)
 {
+    VS_REQUIRE(d_p1 && d_p2 && h_K && h_E, "null argument");
+    VS_REQUIRE(n >= 5, "need at least 5 correspondences");
+    VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
+    VS_REQUIRE(h_K[0] != 0.0 && h_K[4] != 0.0, "singular camera matrix");
+    cudaStream_t s = (cudaStream_t)stream;
     const int per = 10, mp = 5;
+    const double t = thr / ((h_K[0] + h_K[4]) / 2);
+    const float thr2 = (float)(t * t);
     // EMEstimatorCallback has no checkSubset: the subsets are a function of n alone
     std::vector<int> table((size_t)max_iters * mp);
     int n_rows = max_iters;
@@ -438,32 +500,45 @@ static int ransac_e_driver(const void* d_p1, const void* d_p2, int n, float thr2
         }
     }
     if (n_inliers) *n_inliers = 0;
-    DevMem models, nm, counts, tab;
-    GEOM_CUDA(models.alloc((size_t)max_iters * per * 9 * sizeof(double)));
-    GEOM_CUDA(nm.alloc((size_t)max_iters * sizeof(int)));
-    GEOM_CUDA(counts.alloc((size_t)max_iters * per * sizeof(int)));
-    GEOM_CUDA(tab.alloc(table.size() * sizeof(int)));
-    GEOM_CUDA(cudaMemcpy(tab.p, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemset(nm.p, 0, (size_t)max_iters * sizeof(int)));
-    __atomic_fetch_add(&g_vs_launches, 2ull, __ATOMIC_RELAXED);
-    vs_ransac_e_hyp_kernel<<<(n_rows + 31) / 32, 32>>>((const double2*)d_p1, (const double2*)d_p2, tab.as<int>(), n_rows,
-                                                      models.as<double>(), nm.as<int>());
+    // one scratch block: normalised points (2 x n double2), models, model counts, per-iteration counts, subset table
+    const size_t o_q2 = (size_t)n * 16, o_models = 2 * o_q2, o_counts = o_models + (size_t)max_iters * per * 72,
+                 o_nm = o_counts + (size_t)max_iters * per * 4, o_tab = o_nm + (size_t)max_iters * 4,
+                 total = o_tab + table.size() * 4;
+    void* blk = nullptr;
+    int rc = vs_scratch(6, total, &blk);
+    if (rc) return rc;
+    uint8_t* base = (uint8_t*)blk;
+    double2* q1 = (double2*)base;
+    double2* q2 = (double2*)(base + o_q2);
+    double* models = (double*)(base + o_models);
+    int* counts = (int*)(base + o_counts);
+    int* nm = (int*)(base + o_nm);
+    int* tab = (int*)(base + o_tab);
+    const Intr4 K = {h_K[0], h_K[4], h_K[2], h_K[5]};
+    GEOM_CUDA(cudaMemcpyAsync(tab, table.data(), table.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    GEOM_CUDA(cudaMemsetAsync(nm, 0, (size_t)max_iters * sizeof(int), s));
+    __atomic_fetch_add(&g_vs_launches, 4ull, __ATOMIC_RELAXED);
+    vs_normalise_points_kernel<<<(n + 255) / 256, 256, 0, s>>>(K, (const float2*)d_p1, n, q1);
+    vs_normalise_points_kernel<<<(n + 255) / 256, 256, 0, s>>>(K, (const float2*)d_p2, n, q2);
+    if (n_rows > 0)
+        vs_ransac_e_hyp_kernel<<<(n_rows + 31) / 32, 32, 0, s>>>(q1, q2, tab, n_rows, models, nm);
     GEOM_CUDA(cudaGetLastError());
-    vs_score_models_kernel<1><<<max_iters * per, 128>>>(models.as<double>(), nm.as<int>(), per, d_p1, d_p2, n, thr2,
-                                                       counts.as<int>(), nullptr);
+    vs_score_models_kernel<1><<<max_iters * per, 128, 0, s>>>(models, nm, per, q1, q2, n, thr2, counts, nullptr);
     GEOM_CUDA(cudaGetLastError());
     std::vector<int> h_counts((size_t)max_iters * per), h_nm(max_iters);
-    GEOM_CUDA(cudaMemcpy(h_counts.data(), counts.p, h_counts.size() * sizeof(int), cudaMemcpyDeviceToHost));
-    GEOM_CUDA(cudaMemcpy(h_nm.data(), nm.p, h_nm.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    GEOM_CUDA(cudaMemcpyAsync(h_counts.data(), counts, h_counts.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    GEOM_CUDA(cudaMemcpyAsync(h_nm.data(), nm, h_nm.size() * sizeof(int), cudaMemcpyDeviceToHost, s));
+    GEOM_CUDA(cudaStreamSynchronize(s));
     h_nm.resize(n_rows);
-    const int best = ransac_replay(h_counts, h_nm, per, n, mp, conf, max_iters);
+    const int best = ransac_replay(h_counts, h_nm, per, n, mp, prob, max_iters);
     if (best < 0) {
-        for (int e = 0; e < 9; ++e) h_model[e] = 0.0;
-        if (h_mask) memset(h_mask, 0, n);
+        for (int e = 0; e < 9; ++e) h_E[e] = 0.0;
+        if (d_mask) GEOM_CUDA(cudaMemsetAsync(d_mask, 0, n, s));
         return VSLAM_OK;
     }
-    GEOM_CUDA(cudaMemcpy(h_model, models.as<double>() + (size_t)best * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost));
-    return score_common(1, h_model, d_p1, d_p2, n, thr2, h_mask, n_inliers);
+    GEOM_CUDA(cudaMemcpyAsync(h_E, models + (size_t)best * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    GEOM_CUDA(cudaStreamSynchronize(s));
+    return score_points(1, h_E, h_K, d_p1, d_p2, n, thr2, d_mask, n_inliers, s);
 }
 
 extern "C" size_t vslam_ransac_fundamental_batched_workspace(int pairs, int cap)
@@ -498,26 +573,30 @@ extern "C" int vslam_ransac_fundamental_host(const float* h_p1, const float* h_p
     VS_REQUIRE(h_p1 && h_p2 && h_F, "null argument");
     VS_REQUIRE(n >= 7, "need at least 7 correspondences");
     VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
-    // one pair through the batched kernel (same arithmetic, so a batch entry equals a single call)
+    // one pair through the batched kernel (same arithmetic, so a batch entry equals a single call); per-thread
+    // scratch: points (both sets), then F, count + n, mask
     const int cap = n;
-    DevMem pts, F, mask, cnt;
-    GEOM_CUDA(pts.alloc((size_t)2 * cap * sizeof(float2)));
-    GEOM_CUDA(F.alloc(9 * sizeof(double)));
-    GEOM_CUDA(mask.alloc(cap));
-    GEOM_CUDA(cnt.alloc(2 * sizeof(int)));
-    GEOM_CUDA(cudaMemcpy(pts.p, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemcpy(pts.as<float2>() + cap, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
+    const size_t o_F = (size_t)2 * cap * sizeof(float2), o_cnt = o_F + 9 * sizeof(double), o_mask = o_cnt + 2 * sizeof(int);
+    void* blk = nullptr;
+    int rc = vs_scratch(6, o_mask + cap, &blk);
+    if (rc) return rc;
+    uint8_t* base = (uint8_t*)blk;
+    float2* pts = (float2*)base;
+    double* F = (double*)(base + o_F);
+    int* cnt = (int*)(base + o_cnt);
+    uint8_t* mask = base + o_mask;
+    GEOM_CUDA(cudaMemcpy(pts, h_p1, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(pts + cap, h_p2, (size_t)n * 8, cudaMemcpyHostToDevice));
     const int n_eff = n;
-    GEOM_CUDA(cudaMemcpy(cnt.as<int>() + 1, &n_eff, sizeof(int), cudaMemcpyHostToDevice));
+    GEOM_CUDA(cudaMemcpy(cnt + 1, &n_eff, sizeof(int), cudaMemcpyHostToDevice));
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
-    vs_ransac_f_batched_kernel<<<1, FB_THREADS>>>(nullptr, nullptr, 0, nullptr, cnt.as<int>() + 1, cap, (float)(thr * thr),
-                                                  conf, max_iters, seed, 7, pts.as<float2>(), F.as<double>(),
-                                                  mask.as<uint8_t>(), cnt.as<int>());
+    vs_ransac_f_batched_kernel<<<1, FB_THREADS>>>(nullptr, nullptr, 0, nullptr, cnt + 1, cap, (float)(thr * thr),
+                                                  conf, max_iters, seed, 7, pts, F, mask, cnt);
     GEOM_CUDA(cudaGetLastError());
     int c = 0;
-    GEOM_CUDA(cudaMemcpy(&c, cnt.p, sizeof(int), cudaMemcpyDeviceToHost));
-    GEOM_CUDA(cudaMemcpy(h_F, F.p, 9 * sizeof(double), cudaMemcpyDeviceToHost));
-    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, mask.p, n, cudaMemcpyDeviceToHost));
+    GEOM_CUDA(cudaMemcpy(&c, cnt, sizeof(int), cudaMemcpyDeviceToHost));
+    GEOM_CUDA(cudaMemcpy(h_F, F, 9 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, mask, n, cudaMemcpyDeviceToHost));
     if (n_inliers) *n_inliers = c < 0 ? 0 : c;
     return VSLAM_OK;
 }
@@ -528,15 +607,12 @@ extern "C" int vslam_ransac_essential_host(const float* h_p1, const float* h_p2,
 {
     VS_REQUIRE(h_p1 && h_p2 && h_K && h_E, "null argument");
     VS_REQUIRE(n >= 5, "need at least 5 correspondences");
-    VS_REQUIRE(max_iters >= 1 && max_iters <= 100000, "max_iters out of range");
-    std::vector<double> q1, q2;
-    normalise_points(h_p1, n, h_K, q1);
-    normalise_points(h_p2, n, h_K, q2);
-    DevMem a, b;
-    GEOM_CUDA(a.alloc((size_t)n * 16));
-    GEOM_CUDA(b.alloc((size_t)n * 16));
-    GEOM_CUDA(cudaMemcpy(a.p, q1.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
-    GEOM_CUDA(cudaMemcpy(b.p, q2.data(), (size_t)n * 16, cudaMemcpyHostToDevice));
-    double t = thr / ((h_K[0] + h_K[4]) / 2);
-    return ransac_e_driver(a.p, b.p, n, (float)(t * t), prob, max_iters, seed, h_E, h_mask, n_inliers);
+    void *a, *b, *m;
+    int rc = stage_points(h_p1, h_p2, n, &a, &b, &m);
+    if (rc) return rc;
+    rc = vslam_ransac_essential((const float*)a, (const float*)b, n, h_K, prob, thr, max_iters, seed, h_E, (uint8_t*)m,
+                                n_inliers, nullptr);
+    if (rc) return rc;
+    if (h_mask) GEOM_CUDA(cudaMemcpy(h_mask, m, n, cudaMemcpyDeviceToHost));
+    return VSLAM_OK;
 }

@@ -170,20 +170,53 @@ vs_gftt_cell_kernel(const float* __restrict__ eig, int w, int h, int rows, int c
     }
 }
 
-namespace {
-struct DevMem {
-    void* p = nullptr;
-    ~DevMem() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
-    template <class T> T* as() { return (T*)p; }
-};
-}
-
 #define GFTT_CUDA(call)                                                                  \
     do {                                                                                 \
         cudaError_t e__ = (call);                                                        \
         if (e__ != cudaSuccess) return vs_cuda_fail(e__, #call, __FILE__, __LINE__);     \
     } while (0)
+
+// Device form: frame on the device (tightly packed, pitch = width), corners per cell in d_xy
+// [rows*cols][max_per_cell][2] (cell c's corners in acceptance order at row c), d_cell_count [rows*cols];
+// d_status (1 int, may be NULL) is set non-zero when a cell held more local maxima than the candidate staging.
+// The min-eigenvalue maps live in the calling thread's scratch (12 bytes per pixel).
+extern "C" int vslam_gftt_grid(const uint8_t* d_frame, int height, int width, int rows, int cols, int max_per_cell,
+                               double quality, double min_distance, float* d_xy, int32_t* d_cell_count,
+                               int32_t* d_status, void* stream)
+{
+    VS_REQUIRE(d_frame && d_cell_count, "null argument");
+    VS_REQUIRE(height >= 3 && width >= 3 && rows >= 1 && cols >= 1 && rows <= height && cols <= width, "bad geometry");
+    VS_REQUIRE(max_per_cell >= 0 && max_per_cell <= GFTT_MAX_PER_CELL, "max_per_cell out of range (0..1024)");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int cells = rows * cols;
+    GFTT_CUDA(cudaMemsetAsync(d_cell_count, 0, cells * sizeof(int32_t), s));
+    if (d_status) GFTT_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int32_t), s));
+    if (max_per_cell == 0) return VSLAM_OK;
+    VS_REQUIRE(d_xy, "null d_xy");
+    const size_t n = (size_t)width * height;
+    void* blk = nullptr;
+    int rc = vs_scratch(7, n * (sizeof(float2) + sizeof(float)) + 256, &blk);
+    if (rc) return rc;
+    float2* dxy = (float2*)blk;
+    float* eig = (float*)(dxy + n);
+    int32_t* st = d_status ? d_status : (int32_t*)(eig + n);
+    if (!d_status) GFTT_CUDA(cudaMemsetAsync(st, 0, sizeof(int32_t), s));
+    __atomic_fetch_add(&g_vs_launches, 3ull, __ATOMIC_RELAXED);
+    vs_gftt_sobel_kernel<<<dim3((width + 127) / 128, height), 128, 0, s>>>(d_frame, width, height, dxy);
+    vs_gftt_eig_kernel<<<(width + 63) / 64, 64, 0, s>>>(dxy, width, height, eig);
+    const int cell_area = (height / rows) * (width / cols);
+    int cand_cap = cell_area < 20480 ? cell_area : 20480;
+    if (cand_cap < 32) cand_cap = 32;
+    int p2 = 1;
+    while (p2 < cand_cap) p2 <<= 1;
+    const size_t smem = (size_t)p2 * sizeof(unsigned long long);
+    if (smem > 48 * 1024)
+        GFTT_CUDA(cudaFuncSetAttribute(vs_gftt_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    vs_gftt_cell_kernel<<<cells, 256, smem, s>>>(eig, width, height, rows, cols, max_per_cell, quality,
+                                                 min_distance * min_distance, cand_cap, d_xy, d_cell_count, st);
+    GFTT_CUDA(cudaGetLastError());
+    return VSLAM_OK;
+}
 
 extern "C" int vslam_gftt_grid_host(const uint8_t* h_frame, int height, int width, int rows, int cols,
                                     int max_per_cell, double quality, double min_distance, float* h_xy,
@@ -197,36 +230,22 @@ extern "C" int vslam_gftt_grid_host(const uint8_t* h_frame, int height, int widt
     for (int c = 0; c < cells; ++c) h_cell_count[c] = 0;
     if (max_per_cell == 0) return VSLAM_OK;
     VS_REQUIRE(h_xy, "null h_xy");
-    const size_t n = (size_t)width * height;
-    DevMem img, dxy, eig, xy, cnt, st;
-    GFTT_CUDA(img.alloc(n));
-    GFTT_CUDA(dxy.alloc(n * sizeof(float2)));
-    GFTT_CUDA(eig.alloc(n * sizeof(float)));
-    GFTT_CUDA(xy.alloc((size_t)cells * max_per_cell * 2 * sizeof(float)));
-    GFTT_CUDA(cnt.alloc(cells * sizeof(int32_t)));
-    GFTT_CUDA(st.alloc(sizeof(int32_t)));
-    GFTT_CUDA(cudaMemcpy(img.p, h_frame, n, cudaMemcpyHostToDevice));
-    GFTT_CUDA(cudaMemset(st.p, 0, sizeof(int32_t)));
-    g_vs_launches += 3;
-    vs_gftt_sobel_kernel<<<dim3((width + 127) / 128, height), 128>>>(img.as<uint8_t>(), width, height, dxy.as<float2>());
-    vs_gftt_eig_kernel<<<(width + 63) / 64, 64>>>(dxy.as<float2>(), width, height, eig.as<float>());
-    const int cell_area = (height / rows) * (width / cols);
-    int cand_cap = cell_area < 20480 ? cell_area : 20480;
-    if (cand_cap < 32) cand_cap = 32;
-    int p2 = 1;
-    while (p2 < cand_cap) p2 <<= 1;
-    const size_t smem = (size_t)p2 * sizeof(unsigned long long);
-    if (smem > 48 * 1024)
-        GFTT_CUDA(cudaFuncSetAttribute(vs_gftt_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    vs_gftt_cell_kernel<<<cells, 256, smem>>>(eig.as<float>(), width, height, rows, cols, max_per_cell, quality,
-                                              min_distance * min_distance, cand_cap, xy.as<float>(), cnt.as<int32_t>(),
-                                              st.as<int32_t>());
-    GFTT_CUDA(cudaGetLastError());
+    const size_t n = (size_t)width * height, xy_bytes = (size_t)cells * max_per_cell * 2 * sizeof(float);
+    void *img = nullptr, *out = nullptr;
+    int rc;
+    if ((rc = vs_scratch(0, n, &img)) || (rc = vs_scratch(1, xy_bytes + (cells + 1) * sizeof(int32_t), &out))) return rc;
+    float* d_xy = (float*)out;
+    int32_t* d_cnt = (int32_t*)((uint8_t*)out + xy_bytes);
+    int32_t* d_st = d_cnt + cells;
+    GFTT_CUDA(cudaMemcpy(img, h_frame, n, cudaMemcpyHostToDevice));
+    rc = vslam_gftt_grid((const uint8_t*)img, height, width, rows, cols, max_per_cell, quality, min_distance, d_xy, d_cnt,
+                         d_st, nullptr);
+    if (rc) return rc;
     std::vector<float> tmp((size_t)cells * max_per_cell * 2);
     int32_t status = 0;
-    GFTT_CUDA(cudaMemcpy(h_cell_count, cnt.p, cells * sizeof(int32_t), cudaMemcpyDeviceToHost));
-    GFTT_CUDA(cudaMemcpy(tmp.data(), xy.p, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
-    GFTT_CUDA(cudaMemcpy(&status, st.p, sizeof(status), cudaMemcpyDeviceToHost));
+    GFTT_CUDA(cudaMemcpy(h_cell_count, d_cnt, cells * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    GFTT_CUDA(cudaMemcpy(tmp.data(), d_xy, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    GFTT_CUDA(cudaMemcpy(&status, d_st, sizeof(status), cudaMemcpyDeviceToHost));
     if (status) {
         vs_set_error("vslam_gftt_grid_host: more local maxima in a cell than the candidate staging holds");
         return status;

@@ -95,6 +95,64 @@ vs_describe_given_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __r
     desc_out[(size_t)i * 32 + lane] = (uint8_t)byte;
 }
 
+// Device form of the same: keypoints as device arrays in the caller's order.  Row i of desc_out belongs to keypoint
+// i; keep[i] = 1 when the keypoint passes cv2's border test (rounded level-0 point inside [31, W-31) x [31, H-31))
+// and its octave is a planned level, else 0 and the row is zero.
+__global__ void __launch_bounds__(256)
+vs_describe_points_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restrict__ frame, int fpitch,
+                          const uint8_t* __restrict__ pyr, const float* __restrict__ kx, const float* __restrict__ ky,
+                          const float* __restrict__ kangle, const int32_t* __restrict__ koct, int n,
+                          uint8_t* __restrict__ desc_out, uint8_t* __restrict__ keep)
+{
+    __shared__ uint32_t s_pat[256];
+    load_pattern(s_pat);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const float x = kx[i], y = ky[i];
+    const int oct = koct[i];
+    const int rx = __float2int_rn(x), ry = __float2int_rn(y);
+    const bool ok = oct >= 0 && oct < plan.n_levels && rx >= VS_EDGE && rx < plan.width - VS_EDGE && ry >= VS_EDGE &&
+                    ry < plan.height - VS_EDGE;
+    uint32_t byte = 0;
+    if (ok) {
+        const VsLevel& L = plan.lv[oct];
+        const uint8_t* raw;
+        int rpitch;
+        if (oct == 0) { raw = frame; rpitch = fpitch; }
+        else { raw = pyr + L.raw_off; rpitch = L.pitch; }
+        const float inv = __fdiv_rn(1.f, L.scale);
+        const int cx = __float2int_rn(__fmul_rn(x, inv)), cy = __float2int_rn(__fmul_rn(y, inv));
+        const float rad = __fmul_rn(kangle[i], (float)(3.14159265358979323846 / 180.f));
+        const float ca = (float)cos((double)rad), sa = (float)sin((double)rad);
+        byte = brief_byte(pyr + L.blur_off, raw, L.w, L.h, L.pitch, rpitch, cx, cy, ca, sa, s_pat, lane);
+    }
+    desc_out[(size_t)i * 32 + lane] = (uint8_t)byte;
+    if (lane == 0 && keep) keep[i] = ok ? 1 : 0;
+}
+
+extern "C" int vslam_orb_compute(vslam_orb* o, const uint8_t* d_frame, int pitch, const float* d_x, const float* d_y,
+                                 const float* d_angle, const int32_t* d_octave, int n, uint8_t* d_desc,
+                                 uint8_t* d_keep_mask, void* stream)
+{
+    VS_REQUIRE(o && d_frame && n >= 0, "bad argument");
+    if (n == 0) return VSLAM_OK;
+    VS_REQUIRE(d_x && d_y && d_angle && d_octave && d_desc, "null argument");
+    VS_REQUIRE(pitch >= o->prm.width, "pitch smaller than width");
+    const VsPlan& p = o->plan;
+    cudaStream_t s = (cudaStream_t)stream;
+    o->last_stream = s; o->last_frames = d_frame; o->last_pitch = pitch; o->last_batch = 1;
+    o->prof_count = 0;
+    int rc = vs_launch_levels(o, d_frame, 1, pitch, s);           // pyramid + blurred levels of this frame
+    if (rc) return rc;
+    __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
+    vs_describe_points_kernel<<<(n + 7) / 8, 256, 0, s>>>(p, d_frame, pitch, o->d_pyr, d_x, d_y, d_angle, d_octave, n,
+                                                        d_desc, d_keep_mask);
+    VS_CUDA(cudaGetLastError());
+    return VSLAM_OK;
+}
+
 int vs_ensure_host_staging(vslam_orb* o);
 
 extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, const float* h_x, const float* h_y,
@@ -135,9 +193,9 @@ extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, cons
     if (rc) return rc;
     VsGivenKp* d_k = nullptr;
     uint8_t* d_d = nullptr;
-    VS_CUDA(cudaMalloc(&d_k, (size_t)m * sizeof(VsGivenKp)));
-    cudaError_t e = cudaMalloc(&d_d, (size_t)m * 32);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_k, kept.data(), (size_t)m * sizeof(VsGivenKp), cudaMemcpyHostToDevice, s);
+    if ((rc = vs_scratch(0, (size_t)m * sizeof(VsGivenKp), (void**)&d_k)) || (rc = vs_scratch(1, (size_t)m * 32, (void**)&d_d)))
+        return rc;
+    cudaError_t e = cudaMemcpyAsync(d_k, kept.data(), (size_t)m * sizeof(VsGivenKp), cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess) {
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_describe_given_kernel<<<(m + 7) / 8, 256, 0, s>>>(p, o->d_frames, p.width, o->d_pyr, d_k, m, d_d);
@@ -145,8 +203,6 @@ extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, cons
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(h_desc, d_d, (size_t)m * 32, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-    cudaFree(d_k);
-    if (d_d) cudaFree(d_d);
     if (e != cudaSuccess) return vs_cuda_fail(e, "orb_compute", __FILE__, __LINE__);
     memcpy(h_keep_index, keep_idx.data(), (size_t)m * sizeof(int32_t));
     *n_out = m;

@@ -211,11 +211,20 @@ class OrbHandle:
         check(lib().vslam_orb_debug_run_levels_host(self._h, ptr(frames), frames.shape[0]))
 
 
+def _desc32(d):
+    """uint8 [n, 32] descriptors (an empty set may have any trailing shape); anything else is an error, not a reshape."""
+    d = np.ascontiguousarray(d, np.uint8)
+    if d.size == 0:
+        return d.reshape(0, 32)
+    if d.ndim != 2 or d.shape[1] != 32:
+        raise ValueError("descriptors must be uint8 [n, 32] (256-bit ORB), got shape %r" % (d.shape,))
+    return d
+
+
 def bf_knn2_host(q, t):
     """uint8 [nq,32], [nt,32] -> idx int32 [nq,2], dist int32 [nq,2] (-1 = missing)."""
     require_gpu()
-    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
-    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    q, t = _desc32(q), _desc32(t)
     idx = np.full((len(q), 2), -1, np.int32)
     dist = np.full((len(q), 2), -1, np.int32)
     check(lib().vslam_bf_knn2_hamming256_host(ptr(q), len(q), ptr(t), len(t), ptr(idx), ptr(dist)))
@@ -224,9 +233,10 @@ def bf_knn2_host(q, t):
 
 def bf_match_masked_host(q, t, mask=None):
     require_gpu()
-    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
-    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    q, t = _desc32(q), _desc32(t)
     m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    if m is not None and m.shape != (len(q), len(t)):
+        raise ValueError("mask shape %r does not match (%d, %d)" % (m.shape, len(q), len(t)))
     idx = np.full(len(q), -1, np.int32)
     dist = np.full(len(q), -1, np.int32)
     check(lib().vslam_bf_match_masked_host(ptr(q), len(q), ptr(t), len(t), ptr(m), ptr(idx), ptr(dist)))

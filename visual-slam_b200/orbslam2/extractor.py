@@ -151,6 +151,14 @@ class ORBExtractor:
         per_cell = n_features // (rows * cols)
         cv2 = _cv2()
         all_keypoints = []
+        if per_cell <= 0:
+            # cv2.goodFeaturesToTrack(maxCorners=0) means "no limit" (extractor.py:123 with n_features < 64): every
+            # corner above the quality level at >= 10 px from the accepted ones.  A cell cannot hold more than
+            # (cw / 10 + 1) * (ch / 10 + 1) such corners; the kernel's per-cell bound is 1024.
+            bound = (w // cols // 10 + 2) * (h // rows // 10 + 2)
+            if bound > 1024:
+                raise NotImplementedError("distribute_keypoints with n_features < 64 on cells larger than ~300x300 px")
+            per_cell = bound
         if per_cell > 0:
             xy = np.zeros((rows * cols * per_cell, 2), np.float32)
             cc = np.zeros(rows * cols, np.int32)

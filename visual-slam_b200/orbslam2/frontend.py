@@ -144,8 +144,9 @@ def front_end_full(handle, frames, ratio=0.75, threshold=3.0, confidence=0.99, m
                                                          float(confidence), int(max_iters), C.c_uint64(seed),
                                                          ws.data_ptr(), F.data_ptr(), mask.data_ptr(), ninl.data_ptr(), s))
     torch.cuda.synchronize()
+    _native.check(L.vslam_orb_last_status(handle.handle))       # retain-best tie overflow -> VSLAM_E_CAPACITY, loudly
     kp_np = kp.cpu().numpy().view(_native.KP_DTYPE).reshape(B, cap)
-    return {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy(),
+    return {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy().clip(max=cap),
             "match": match[:pairs].cpu().numpy(), "match_count": mcount[:pairs].cpu().numpy(),
             "F": F[:pairs].cpu().numpy().reshape(pairs, 3, 3), "mask": mask[:pairs].cpu().numpy(),
             "n_inliers": ninl[:pairs].cpu().numpy()}
@@ -204,8 +205,9 @@ def track_batched(handle, frames, camera_matrix, ratio=0.75, threshold_percent=0
                                             E.data_ptr(), rmask.data_ptr(), pmask.data_ptr(), R.data_ptr(),
                                             t.data_ptr(), status.data_ptr(), s))
     torch.cuda.synchronize()
+    _native.check(L.vslam_orb_last_status(handle.handle))       # retain-best tie overflow -> VSLAM_E_CAPACITY, loudly
     kp_np = kp.cpu().numpy().view(_native.KP_DTYPE).reshape(B, cap)
-    out = {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy(),
+    out = {"kp": kp_np, "desc": desc.cpu().numpy(), "count": count.cpu().numpy().clip(max=cap),
            "track_match": tmatch[:pairs].cpu().numpy(), "track_count": tcount[:pairs].cpu().numpy(),
            "E": E[:pairs].cpu().numpy().reshape(pairs, 3, 3), "R": R[:pairs].cpu().numpy().reshape(pairs, 3, 3),
            "t": t[:pairs].cpu().numpy().reshape(pairs, 3, 1), "ransac_mask": rmask[:pairs].cpu().numpy(),
@@ -323,6 +325,38 @@ class _Cv2Proxy:
         return find_fundamental_ransac(np.asarray(points1, np.float32).reshape(-1, 2),
                                        np.asarray(points2, np.float32).reshape(-1, 2),
                                        ransacReprojThreshold, confidence, maxIters)
+
+
+    def findEssentialMat(self, points1, points2, cameraMatrix=None, method=None, prob=0.999, threshold=1.0,
+                         maxIters=1000, mask=None):
+        """cv2.findEssentialMat(p1, p2, K, RANSAC, prob, threshold) as Tracker._track_from_last_frame calls it
+        (tracker.py:242) -> (E float64 [3,3] or None, mask uint8 [n,1])."""
+        cv2 = self._cv2
+        if method is None:
+            method = cv2.RANSAC
+        if method != cv2.RANSAC or cameraMatrix is None or len(points1) < 5:
+            raise NotImplementedError("findEssentialMat on the B200 kernels: RANSAC with a camera matrix, >= 5 points")
+        from .utils import calculate_essential_matrix
+        return calculate_essential_matrix(points1, points2, cameraMatrix, prob=prob, threshold=threshold,
+                                          max_iters=maxIters)
+
+    def recoverPose(self, E, points1, points2, cameraMatrix=None, mask=None, **kw):
+        """cv2.recoverPose(E, p1, p2, K, mask=mask) (tracker.py:249) -> (n_inliers, R, t, mask)."""
+        if cameraMatrix is None or kw:
+            raise NotImplementedError("recoverPose on the B200 kernels: the (E, points1, points2, cameraMatrix, mask) form")
+        from .utils import recover_pose
+        return recover_pose(E, points1, points2, cameraMatrix, mask)
+
+
+def install_tracker_adaptor(module):
+    """Point `module.cv2` (the reference's `orbslam2.tracker`) at the proxy: Tracker._track_from_last_frame calls
+    cv2.findEssentialMat / cv2.recoverPose directly (tracker.py:242,249), so swapping the extractor / matcher /
+    initializer classes alone leaves those two on the CPU.  Drawing calls stay cv2's.  Undo: module.cv2 = proxy._cv2."""
+    import cv2
+    _native.require_gpu()
+    proxy = _Cv2Proxy(cv2)
+    module.cv2 = proxy
+    return proxy
 
 
 def install_local_mapper_adaptor(module):

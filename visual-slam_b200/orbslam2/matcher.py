@@ -65,6 +65,10 @@ class DescriptorMatcher:
         d2 = np.ascontiguousarray(descriptors2, np.uint8)
         if d1.shape[0] == 0 or d2.shape[0] == 0:
             return []
+        if mask is not None:
+            mask = np.asarray(mask)
+            if mask.shape != (d1.shape[0], d2.shape[0]):       # cv2 asserts on this; the C side would read out of bounds
+                raise ValueError("mask shape %r does not match (%d, %d)" % (mask.shape, d1.shape[0], d2.shape[0]))
         idx, dist = _native.bf_match_masked_host(d1, d2, mask)
         cv2 = _cv2()
         matches = [cv2.DMatch(int(q), int(idx[q]), 0, float(dist[q])) for q in range(len(idx)) if idx[q] >= 0]
