@@ -62,3 +62,29 @@ def golden_path(name):
 
 def load_golden(name):
     return np.load(golden_path(name), allow_pickle=False)
+
+
+def canonical_kp_hash(x, y, size, angle, response, octave, desc):
+    """sha256 of a keypoint set in canonical order (octave, y, x) -- the construction of
+    tests/golden/make_fixture_golden.py: every cv2.KeyPoint field as float32 / int32 plus the descriptor bytes."""
+    import hashlib
+    x, y = np.asarray(x, np.float32), np.asarray(y, np.float32)
+    o = np.asarray(octave, np.int32)
+    order = np.lexsort((x, y, o))
+    h = hashlib.sha256()
+    for c in (x, y, np.asarray(size, np.float32), np.asarray(angle, np.float32), np.asarray(response, np.float32), o):
+        h.update(np.ascontiguousarray(c[order]).tobytes())
+    h.update(np.ascontiguousarray(np.asarray(desc, np.uint8)[order]).tobytes())
+    return np.frombuffer(h.digest(), np.uint8)
+
+
+def fixture_image(pair, which):
+    """gray fixture image (tests/golden/fixture_images: the reference's own BGR2GRAY of its data/ images)"""
+    import cv2
+    img = cv2.imread(os.path.join(GOLDEN, "fixture_images", "%s_img%d.png" % (pair, which)), cv2.IMREAD_UNCHANGED)
+    assert img is not None and img.ndim == 2 and img.dtype == np.uint8
+    return img
+
+
+def match_row_set(rows):
+    return {tuple(float(v) for v in r) for r in np.asarray(rows, np.float32).reshape(-1, 7)}

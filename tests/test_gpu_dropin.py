@@ -67,6 +67,56 @@ def test_real_bgr_images_and_match_lists(pair):
     assert len(ms2) == len(ms)
 
 
+@pytest.mark.parametrize("pair", ["pair%02d" % i for i in range(1, 21)])
+def test_every_fixture_image_equals_reference(pair):
+    """All 40 fixture images through the drop-in ORBExtractor / DescriptorMatcher: keypoints (every field) and
+    descriptors hash to the reference's, the match list equals the reference's as a set of rows (up to a handful of
+    equal-distance ties, which cv2 breaks by its unspecified in-level keypoint order)."""
+    from conftest import canonical_kp_hash, fixture_image, match_row_set
+    from orbslam2.extractor import ORBExtractor
+    from orbslam2.matcher import DescriptorMatcher
+    g = load_golden("fixtures_all.npz")
+    ex = ORBExtractor(n_features=2000)
+    res = []
+    for w in (1, 2):
+        kps, desc = ex.detect_and_compute(fixture_image(pair, w))
+        assert len(kps) == int(g["%s_img%d_n" % (pair, w)])
+        hsh = canonical_kp_hash([k.pt[0] for k in kps], [k.pt[1] for k in kps], [k.size for k in kps],
+                                [k.angle for k in kps], [k.response for k in kps], [k.octave for k in kps], desc)
+        assert np.array_equal(hsh, g["%s_img%d_sha" % (pair, w)])
+        res.append((kps, desc))
+    (k1, d1), (k2, d2) = res
+    ms = DescriptorMatcher(ratio_threshold=0.75).match(d1, d2)
+    rows = [(k1[m.queryIdx].pt[0], k1[m.queryIdx].pt[1], k1[m.queryIdx].octave, k2[m.trainIdx].pt[0],
+             k2[m.trainIdx].pt[1], k2[m.trainIdx].octave, m.distance) for m in ms]
+    got, ref = match_row_set(rows), match_row_set(g[pair + "_match75"])
+    assert len(got ^ ref) <= 6, (len(got), len(ref), len(got ^ ref))
+
+
+@pytest.mark.parametrize("tag,w,h,nf", [("c3", 1920, 1080, 8000), ("c5", 3840, 2160, 16000)])
+def test_c3_and_c5_size_frames_equal_reference(tag, w, h, nf):
+    """Reference-made goldens at the sizes of BASELINE configs 3 and 5."""
+    from conftest import canonical_kp_hash, match_row_set
+    from orbslam2 import _native
+    from orbslam2.synth import SyntheticVideo
+    g = load_golden("fixtures_all.npz")
+    v = SyntheticVideo(w, h, 0)
+    frames = v.frames(0, 2)
+    hd = _native.OrbHandle(w, h, n_features=nf, max_batch=2)
+    kp, desc, cnt, match, mc = hd.frontend_host(frames, 0.75)
+    for k in (0, 1):
+        n = int(cnt[k])
+        assert n == int(g["%s_kp%d_n" % (tag, k)])
+        a = kp[k][:n]
+        assert np.array_equal(canonical_kp_hash(a["x"], a["y"], a["size"], a["angle"], a["response"], a["octave"], desc[k][:n]),
+                              g["%s_kp%d_sha" % (tag, k)])
+    rows = [(kp[0]["x"][q], kp[0]["y"][q], kp[0]["octave"][q], kp[1]["x"][t], kp[1]["y"][t], kp[1]["octave"][t], d)
+            for q, t, d in match[0][:mc[0]]]
+    got, ref = match_row_set(rows), match_row_set(g[tag + "_match75"])
+    assert len(got ^ ref) <= 12, (len(got), len(ref), len(got ^ ref))
+    hd.close()
+
+
 def test_gt_matcher_procedure_and_compute():
     """src/tests/gt_test_matcher.py on the committed pairs: compute() at hand-labelled keypoints
     then match(0.85) -> the reference's exact match list."""

@@ -173,6 +173,45 @@ def test_ransac_replay_equals_reference_on_long_runs():
             assert np.array_equal(mask, g["small%d_Fmask" % j] != 0)
 
 
+@pytest.mark.parametrize("pair", ["pair%02d" % i for i in range(1, 21)])
+def test_oracle_equals_reference_on_every_fixture_image(oracle, pair):
+    """All 40 fixture images (tests/golden/make_fixture_golden.py): the oracle's keypoint set -- every field, every
+    descriptor byte -- hashes to what the reference returned, and its match list is the reference's as a set of
+    (pt1, octave1, pt2, octave2, distance) rows."""
+    from conftest import canonical_kp_hash, fixture_image, match_row_set
+    g = load_golden("fixtures_all.npz")
+    res = []
+    for w in (1, 2):
+        r = oracle.orb_detect_and_compute(fixture_image(pair, w), 2000)
+        assert len(r["x"]) == int(g["%s_img%d_n" % (pair, w)])
+        assert np.array_equal(canonical_kp_hash(r["x"], r["y"], r["size"], r["angle"], r["response"], r["octave"], r["desc"]),
+                              g["%s_img%d_sha" % (pair, w)])
+        res.append(r)
+    ms = oracle.match(res[0]["desc"], res[1]["desc"], 0.75)
+    a, b = res
+    rows = [(a["x"][q], a["y"][q], a["octave"][q], b["x"][t], b["y"][t], b["octave"][t], d) for q, t, d in ms]
+    got, ref = match_row_set(rows), match_row_set(g[pair + "_match75"])
+    # equal-distance ties between train descriptors are broken by index, and the in-level keypoint order is the one
+    # thing cv2 leaves unspecified: allow the handful of rows that differ by such a tie, no more
+    assert len(got ^ ref) <= 6, (len(got), len(ref), len(got ^ ref))
+
+
+@pytest.mark.parametrize("tag,w,h,nf", [("c3", 1920, 1080, 8000), ("c5", 3840, 2160, 16000)])
+def test_oracle_equals_reference_at_c3_and_c5_size(oracle, tag, w, h, nf):
+    """Reference-made goldens at the sizes of BASELINE configs 3 and 5 (the frames are regenerated here)."""
+    from conftest import canonical_kp_hash
+    from orbslam2.synth import SyntheticVideo
+    g = load_golden("fixtures_all.npz")
+    v = SyntheticVideo(w, h, 0)
+    for k in (0, 1):
+        f = v.frame(k)
+        assert bytes(g["%s_frame%d_sha" % (tag, k)]) == hashlib.sha256(f.tobytes()).digest()
+        r = oracle.orb_detect_and_compute(f, nf)
+        assert len(r["x"]) == int(g["%s_kp%d_n" % (tag, k)])
+        assert np.array_equal(canonical_kp_hash(r["x"], r["y"], r["size"], r["angle"], r["response"], r["octave"], r["desc"]),
+                              g["%s_kp%d_sha" % (tag, k)])
+
+
 def test_orbslam2_oracle_invariants():
     """oracle/orbslam2_oracle.py (parity unpinned: the reference has no such mode): the quadtree keeps one
     corner per node, never more than quota + 3 nodes once past the first round, all of them when the quota
