@@ -33,32 +33,26 @@ extern "C" int vslam_ratio_filter(const int32_t* d_idx, const int32_t* d_dist, i
                            (cudaStream_t)stream);
 }
 
-namespace {
-struct DevBuf {
-    void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t n) { VS_CUDA(cudaMalloc(&p, n ? n : 16)); return VSLAM_OK; }
-};
-}
-
+// host-buffer forms: descriptors and results staged in the calling thread's scratch (no cudaMalloc per call)
 extern "C" int vslam_bf_knn2_hamming256_host(const uint8_t* h_query, int nq, const uint8_t* h_train, int nt,
                                              int32_t* h_idx, int32_t* h_dist)
 {
     VS_REQUIRE(nq >= 0 && nt >= 0, "negative size");
     if (nq == 0) return VSLAM_OK;
     VS_REQUIRE(h_query && h_idx && h_dist && (h_train || nt == 0), "null argument");
-    DevBuf q, t, i, d;
+    void *q, *t, *i;
     int rc;
-    if ((rc = q.alloc((size_t)nq * 32)) || (rc = t.alloc((size_t)nt * 32)) ||
-        (rc = i.alloc((size_t)nq * 8)) || (rc = d.alloc((size_t)nq * 8)))
+    if ((rc = vs_scratch(0, (size_t)nq * 32, &q)) || (rc = vs_scratch(1, (size_t)nt * 32, &t)) ||
+        (rc = vs_scratch(2, (size_t)nq * 16, &i)))
         return rc;
-    VS_CUDA(cudaMemcpy(q.p, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
-    if (nt) VS_CUDA(cudaMemcpy(t.p, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
-    rc = vs_launch_knn2(nullptr, (const uint8_t*)q.p, nq, nq, (const uint8_t*)t.p, nt, nt, nullptr, nullptr, 1,
-                        (int32_t*)i.p, (int32_t*)d.p, 0);
+    int32_t* d_idx = (int32_t*)i;
+    int32_t* d_dist = d_idx + (size_t)nq * 2;
+    VS_CUDA(cudaMemcpy(q, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    if (nt) VS_CUDA(cudaMemcpy(t, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
+    rc = vs_launch_knn2(nullptr, (const uint8_t*)q, nq, nq, (const uint8_t*)t, nt, nt, nullptr, nullptr, 1, d_idx, d_dist, 0);
     if (rc) return rc;
-    VS_CUDA(cudaMemcpy(h_idx, i.p, (size_t)nq * 8, cudaMemcpyDeviceToHost));
-    VS_CUDA(cudaMemcpy(h_dist, d.p, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_idx, d_idx, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_dist, d_dist, (size_t)nq * 8, cudaMemcpyDeviceToHost));
     return VSLAM_OK;
 }
 
@@ -68,22 +62,23 @@ extern "C" int vslam_bf_match_masked_host(const uint8_t* h_query, int nq, const 
     VS_REQUIRE(nq >= 0 && nt >= 0, "negative size");
     if (nq == 0) return VSLAM_OK;
     VS_REQUIRE(h_query && h_idx && h_dist && (h_train || nt == 0), "null argument");
-    DevBuf q, t, m, i, d;
+    void *q, *t, *i, *m = nullptr;
     int rc;
-    if ((rc = q.alloc((size_t)nq * 32)) || (rc = t.alloc((size_t)nt * 32)) ||
-        (rc = i.alloc((size_t)nq * 4)) || (rc = d.alloc((size_t)nq * 4)))
+    if ((rc = vs_scratch(0, (size_t)nq * 32, &q)) || (rc = vs_scratch(1, (size_t)nt * 32, &t)) ||
+        (rc = vs_scratch(2, (size_t)nq * 8, &i)))
         return rc;
-    VS_CUDA(cudaMemcpy(q.p, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
-    if (nt) VS_CUDA(cudaMemcpy(t.p, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
+    int32_t* d_idx = (int32_t*)i;
+    int32_t* d_dist = d_idx + nq;
+    VS_CUDA(cudaMemcpy(q, h_query, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    if (nt) VS_CUDA(cudaMemcpy(t, h_train, (size_t)nt * 32, cudaMemcpyHostToDevice));
     if (h_mask) {
-        if ((rc = m.alloc((size_t)nq * nt))) return rc;
-        if (nt) VS_CUDA(cudaMemcpy(m.p, h_mask, (size_t)nq * nt, cudaMemcpyHostToDevice));
+        if ((rc = vs_scratch(3, (size_t)nq * nt, &m))) return rc;
+        if (nt) VS_CUDA(cudaMemcpy(m, h_mask, (size_t)nq * nt, cudaMemcpyHostToDevice));
     }
-    rc = vs_launch_match_masked((const uint8_t*)q.p, nq, (const uint8_t*)t.p, nt,
-                                h_mask ? (const uint8_t*)m.p : nullptr, (int32_t*)i.p, (int32_t*)d.p, 0);
+    rc = vs_launch_match_masked((const uint8_t*)q, nq, (const uint8_t*)t, nt, (const uint8_t*)m, d_idx, d_dist, 0);
     if (rc) return rc;
-    VS_CUDA(cudaMemcpy(h_idx, i.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
-    VS_CUDA(cudaMemcpy(h_dist, d.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_idx, d_idx, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    VS_CUDA(cudaMemcpy(h_dist, d_dist, (size_t)nq * 4, cudaMemcpyDeviceToHost));
     return VSLAM_OK;
 }
 

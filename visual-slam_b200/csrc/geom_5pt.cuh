@@ -189,7 +189,7 @@ VS_HD VS_NOINLINE double polish_5pt(const double L[9][4], double c[4], double* s
     double E[9], f[11], EEt[9], tr;
     double r2 = polish_residual(L, c, E, f, EEt, &tr);
     *start_r2 = r2;
-    for (int it = 0; it < 12 && r2 > 1e-30 && isfinite(r2); ++it) {
+    for (int it = 0; it < 12 && r2 > 1e-26 && isfinite(r2); ++it) {
 #ifdef VS_POLISH_TRACE
         VS_POLISH_TRACE(it, r2, c);
 #endif
@@ -266,8 +266,10 @@ VS_HD VS_NOINLINE double polish_5pt(const double L[9][4], double c[4], double* s
 
 // One pass of Nister's elimination in the null-space basis nb (orthonormal rows): appends the polished real solutions
 // that are not yet in E[0..n) and returns the new count.  *trouble is set when the pass cannot be trusted to be
-// complete: a root of the degree-10 polynomial started far from a solution (the elimination lost digits), two roots
-// polished into one solution (so another one was probably missed), or a polish did not converge.
+// complete: a polish did not converge, two roots polished into one solution (so another one was probably missed),
+// leading coefficients vanished (roots at infinity of this chart), or the number of solutions found is odd.  (A start
+// value far from its solution is NOT a trigger: on a panning camera the elimination loses digits on every second
+// sample, the polish recovers them, and nothing is missed.)
 VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int n, bool* trouble)
 {
     const int have_before = n;
@@ -397,7 +399,6 @@ VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int 
         }
         double r_start;
         const double r_end = polish_5pt(L, cc, &r_start);
-        if (!(r_start < 1e-12)) *trouble = true;
         if (!(r_end < 1e-16)) { *trouble = true; continue; }       // not a solution of the constraints
         double Ek[9], nrm = 0.0;
         for (int e = 0; e < 9; ++e) {
@@ -420,6 +421,9 @@ VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int 
         for (int e = 0; e < 9; ++e) E[n][e] = Ek[e] * nrm;
         ++n;
     }
+    // the degree-10 polynomial has real coefficients: its real roots come in an even number (with multiplicity).
+    // An odd count of distinct solutions after the first pass means one was missed or two collapsed.
+    if (have_before <= 0 && (n & 1)) *trouble = true;
     return n;
 }
 
@@ -439,19 +443,24 @@ VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double 
         A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
     }
     null_space_9<5>(A, nb);
+    // First pass in a rotated basis (a fixed orthogonal 4 x 4 mix of the Gauss-Jordan basis): the un-mixed basis is
+    // aligned with the coordinate structure of the constraint rows, and for pure sideways motion (a panning camera)
+    // that puts solutions at infinity of the (x, y, z, 1) chart on almost every second sample; mixed, that alignment
+    // is gone and the second pass -- in the un-mixed basis -- is needed for the rare clustered-root cases only
+    // (44 % -> see profiles/r2_ransac_agreement.txt of the samples of the synthetic pan clip needed two passes before).
+    double rb[4][9];
+    for (int e = 0; e < 9; ++e) {
+        const double a = nb[0][e], b = nb[1][e], c = nb[2][e], d = nb[3][e];
+        rb[0][e] = 0.5 * (a + b + c + d);
+        rb[1][e] = 0.5 * (a - b + c - d);
+        rb[2][e] = 0.5 * (a + b - c - d);
+        rb[3][e] = 0.5 * (a - b - c + d);
+    }
     bool trouble = false;
-    int n = solve_5pt_in_basis(nb, E, 0, &trouble);
+    int n = solve_5pt_in_basis(rb, E, 0, &trouble);
     if (trouble) {
-        double rb[4][9];
-        for (int e = 0; e < 9; ++e) {
-            const double a = nb[0][e], b = nb[1][e], c = nb[2][e], d = nb[3][e];
-            rb[0][e] = 0.5 * (a + b + c + d);
-            rb[1][e] = 0.5 * (a - b + c - d);
-            rb[2][e] = 0.5 * (a + b - c - d);
-            rb[3][e] = 0.5 * (a - b - c + d);
-        }
         bool t2 = false;
-        n = solve_5pt_in_basis(rb, E, n, &t2);
+        n = solve_5pt_in_basis(nb, E, n, &t2);
     }
     return n;
 }

@@ -65,9 +65,12 @@ class ORBExtractor:
 
     @staticmethod
     def _keypoints(kp, n):
+        """structured rows -> tuple of cv2.KeyPoint.  Column lists + map(): the constructor calls are the floor
+        (~0.35 us each); per-row field access on the structured array cost five times that."""
         cv2 = _cv2()
-        return tuple(cv2.KeyPoint(float(k["x"]), float(k["y"]), float(k["size"]), float(k["angle"]),
-                                  float(k["response"]), int(k["octave"]), -1) for k in kp[:n])
+        k = kp[:n]
+        return tuple(map(cv2.KeyPoint, k["x"].tolist(), k["y"].tolist(), k["size"].tolist(), k["angle"].tolist(),
+                         k["response"].tolist(), k["octave"].tolist()))
 
     # ---------------------------------------------------------------------- API
     def detect_and_compute(self, image):

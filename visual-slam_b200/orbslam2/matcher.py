@@ -55,7 +55,9 @@ class DescriptorMatcher:
         else:
             keep = two | one
         cv2 = _cv2()
-        return [cv2.DMatch(int(q), int(idx[q, 0]), 0, float(dist[q, 0])) for q in np.nonzero(keep)[0]]
+        q = np.nonzero(keep)[0]
+        # column lists + map(): the cv2.DMatch constructor is the floor; numpy scalar indexing per row doubled it
+        return list(map(cv2.DMatch, q.tolist(), idx[q, 0].tolist(), [0] * len(q), dist[q, 0].astype(np.float32).tolist()))
 
     def match_with_mask(self, descriptors1, descriptors2, mask):
         """matcher.py:85-107: k = 1 restricted by mask, sorted by distance (stable)."""
