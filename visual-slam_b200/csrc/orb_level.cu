@@ -31,6 +31,7 @@
 #define SC_S 72                       // score row stride; column index = tx + 4
 #define BL_ROWS (VS_TH + 6)
 #define LIST_CAP ((VS_TW / 2) * (VS_TH / 2))   // NMS leaves at most one corner per 2x2 block
+#define L0_BOX_W 96                   // level-0 TMA box: columns x0-16 .. x0+79 (16-byte aligned start, tile = x0-4 .. x0+67)
 #ifndef VS_LEVEL_CTAS
 #define VS_LEVEL_CTAS 6                // resident CTAs per SM the register budget is capped for (40 registers)
 #endif
@@ -220,8 +221,17 @@ __device__ __forceinline__ void blur_col_item(const float* p, uint32_t& out0, ui
 }
 
 // L0 = true: level 0 (tile widened from the frame); false: levels >= 1 (tile resized from level - 1).
-// Two instantiations so that each gets its own register allocation and schedule.
-template <bool L0>
+// PWC: row pitch of the staged parent region when it is known at compile time (112 bytes at the reference's scale
+// factor 1.2, whatever the frame size), 0 = read it from the plan.  With PWC fixed the two resize passes are
+// straight-line code: every address is base + immediate and the per-thread trip counts are constants (the generic
+// loops spent as many instructions on their bookkeeping as on the blend: 0.5 of 1.9 warp-instructions per pixel).
+// Separate instantiations so that each gets its own register allocation and schedule.
+#define VS_PAR_W_STD 112
+#ifndef VS_RESIZE_UNROLL
+#define VS_RESIZE_UNROLL 6             // full unrolling (5 / 6 predicated rows per thread): 4.31 vs 4.38 ms per step with 2
+#endif
+constexpr int kResizeUnroll = VS_RESIZE_UNROLL;
+template <bool L0, int PWC>
 __global__ void __launch_bounds__(256, VS_LEVEL_CTAS)
 vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* __restrict__ frames,
                 int fpitch, size_t fstride, uint8_t* __restrict__ pyr,
@@ -253,7 +263,59 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     if (tid == 0) { s_nq = 0; s_n = 0; }
 
     // ---- 1. raw tile (16-bit lanes) ------------------------------------------
-    if (L0) {
+    if (L0 && use_tma) {
+        // Level 0 by TMA, like the parent regions of the other levels: one thread issues a (L0_BOX_W x RAW_H) u8 box
+        // at (x0 - 16, y0 - 4, frame) -- a box must start on a 16-byte boundary, the tile starts at x0 - 4 -- and the
+        // CTA widens it to 16-bit lanes from shared memory.  Pixels outside the frame arrive as zeros; border tiles
+        // read their REFLECT_101 halo from the mirrored position inside the same box (the halo is 4 wide, the box has
+        // 12 spare columns on either side).
+        __shared__ __align__(128) uint8_t s_box[L0_BOX_W * RAW_H];
+        if (tid == 0) {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_box);
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(L0_BOX_W * RAW_H) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"(dst), "l"((uint64_t)&tmap), "r"(x0 - 16), "r"(y0 - VS_HALO), "r"(b), "r"(bar) : "memory");
+        }
+        __syncthreads();
+        {
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_mbar);
+            asm volatile(
+                "{\n .reg .pred p;\n"
+                "W%=: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n"
+                " @p bra D%=;\n bra W%=;\n"
+                "D%=:\n}\n" ::"r"(bar) : "memory");
+        }
+        const int wd = tid % (RAW_W / 4), rg = tid / (RAW_W / 4);        // 18 word columns x 14 row groups
+        const bool interior = x0 >= VS_HALO && x0 + VS_TW + VS_HALO <= W && y0 >= VS_HALO && y0 + VS_TH + VS_HALO <= H;
+        if (rg < 14) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int r = rg + 14 * k;
+                if (r < RAW_H) {
+                    uint32_t u;
+                    if (interior) {
+                        u = *(const uint32_t*)(s_box + r * L0_BOX_W + 12 + 4 * wd);
+                    } else {
+                        // mirrored row / columns, clamped into the box where the pixel cannot matter (beyond the halo)
+                        const int gy = y0 - VS_HALO + r;
+                        const int br = min(max((H - 1) - abs((H - 1) - abs(gy)) - (y0 - VS_HALO), 0), RAW_H - 1);
+                        const uint8_t* row = s_box + br * L0_BOX_W;
+                        u = 0;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int gx = x0 - VS_HALO + 4 * wd + j;
+                            const int bc = min(max((W - 1) - abs((W - 1) - abs(gx)) - (x0 - 16), 0), L0_BOX_W - 1);
+                            u |= (uint32_t)row[bc] << (8 * j);
+                        }
+                    }
+                    *(uint2*)(s_raw + r * RAW_S + 4 * wd) = make_uint2(__byte_perm(u, 0, 0x4140), __byte_perm(u, 0, 0x4342));
+                }
+            }
+        }
+    } else if (L0) {
         const uint8_t* src = frames + (size_t)b * fstride;
         const bool aligned = (((size_t)src | (size_t)fpitch) & 3) == 0;
         // thread = one 4-pixel word column x up to 3 rows; the loads are issued before any store
@@ -297,7 +359,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         else { src = fpyr + P.raw_off; sp = P.pitch; }
         const bool aligned = (((size_t)src | (size_t)sp) & 3) == 0;
         const int sw = P.w, sh = P.h;
-        const int PW = plan.par_w;
+        const int PW = PWC ? PWC : plan.par_w;
         // dynamic smem: [par_h][par_w] parent pixels (128-byte aligned for TMA), then the horizontal pass
         // (offset arithmetic on s_dyn, not on a generic address, so that the accesses stay LDS/STS)
         uint8_t* s_par = s_dyn + ((128u - ((uint32_t)__cvta_generic_to_shared(s_dyn) & 127u)) & 127u);
@@ -330,7 +392,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             uint32_t* dst = isx ? s_tx : s_ty;
             for (int c = lane; c < n; c += 32) dst[c] = __ldg(t + vs_reflect101(o0 + c, lim));
         }
-        if (!use_tma) {   // fallback (unaligned frames, very large scale factors): thread = one word column x every G-th row
+        if (PWC == 0 && !use_tma) {   // fallback (unaligned frames, very large scale factors; only in the generic instantiation): thread = one word column x every G-th row
             const int nwords = (px_hi - pxa) / 4 + 1;
             const int PWW = PW >> 2, G = 256 / PWW;
             const int wd = tid % PWW, rg = tid / PWW;
@@ -370,26 +432,30 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 "D%=:\n}\n" ::"r"(bar) : "memory");
         }
         // separable INTER_LINEAR_EXACT, vertical pass first (the weights are exact integers, so the order of
-        // the two passes does not change the result).  Vertical: thread = one output row x every 6th parent
-        // word; four bytes of parent rows j0 / j1 are widened to 16-bit lanes and blended two at a time --
+        // the two passes does not change the result).  Vertical: thread = one parent word column x every G-th
+        // output row; four bytes of parent rows j0 / j1 are widened to 16-bit lanes and blended two at a time --
         // a lane holds at most 255 * 256, so the packed multiply-adds cannot carry between lanes.
         {
-            const int row = tid / 6, w0 = tid - 6 * row;
-            if (row < RAW_H) {
-                const uint32_t e = s_ty[row];
-                const int j0 = (int)(e & 0xffff);
-                const uint32_t bq = e >> 16, wq = 256u - bq;
-                const int j1 = min(j0 + 1, sh - 1);
-                const uint32_t* pa = (const uint32_t*)(s_par + (j0 - py0) * PW);
-                const uint32_t* pb = (const uint32_t*)(s_par + (j1 - py0) * PW);
-                uint2* dst = (uint2*)(s_v + row * PW);
-                const int nwords = min((px_hi + 1 - pxa) / 4 + 1, PW >> 2);
-#pragma unroll 4
-                for (int wc = w0; wc < nwords; wc += 6) {
-                    const uint32_t ua = pa[wc], ub = pb[wc];
-                    const uint32_t lo = __byte_perm(ua, 0, 0x4140) * wq + __byte_perm(ub, 0, 0x4140) * bq;
-                    const uint32_t hi = __byte_perm(ua, 0, 0x4342) * wq + __byte_perm(ub, 0, 0x4342) * bq;
-                    dst[wc] = make_uint2(lo, hi);
+            const int PWW = PW >> 2, G = 256 / PWW;                        // 28 word columns x 9 row groups at PW = 112
+            const int wc = tid % PWW, rg = tid / PWW;
+            const int nwords = min((px_hi + 1 - pxa) / 4 + 1, PWW);
+            if (rg < G && wc < nwords) {
+                const uint32_t* par32 = (const uint32_t*)s_par + wc;
+                uint2* dst = (uint2*)s_v + wc;
+                const int VIT = PWC ? (RAW_H + (256 / (PWC / 4)) - 1) / (256 / (PWC / 4)) : RAW_H;   // 5 at PW = 112
+#pragma unroll kResizeUnroll
+                for (int k = 0; k < VIT; ++k) {
+                    const int row = rg + k * G;
+                    if (row < RAW_H) {
+                        const uint32_t e = s_ty[row];
+                        const int j0 = (int)(e & 0xffff);
+                        const uint32_t bq = e >> 16, wq = 256u - bq;
+                        const int j1 = min(j0 + 1, sh - 1);
+                        const uint32_t ua = par32[(j0 - py0) * PWW], ub = par32[(j1 - py0) * PWW];
+                        const uint32_t lo = __byte_perm(ua, 0, 0x4140) * wq + __byte_perm(ub, 0, 0x4140) * bq;
+                        const uint32_t hi = __byte_perm(ua, 0, 0x4342) * wq + __byte_perm(ub, 0, 0x4342) * bq;
+                        dst[row * PWW] = make_uint2(lo, hi);
+                    }
                 }
             }
         }
@@ -401,13 +467,16 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             const uint32_t ea = s_tx[2 * cp], eb = s_tx[2 * cp + 1];
             const int ia = (int)(ea & 0xffff) - pxa, ib = (int)(eb & 0xffff) - pxa;
             const uint32_t aa = ea >> 16, ab = eb >> 16, wa = 256u - aa, wb = 256u - ab;
-            uint32_t* s_raw32 = (uint32_t*)s_raw;
-#pragma unroll 2
-            for (int r = rg7; r < RAW_H; r += 7) {
-                const uint16_t* v = s_v + r * PW;
-                const uint32_t lo = (uint32_t)v[ia] * wa + (uint32_t)v[ia + 1] * aa + 32768u;
-                const uint32_t hi = (uint32_t)v[ib] * wb + (uint32_t)v[ib + 1] * ab + 32768u;
-                s_raw32[r * (RAW_S / 2) + cp] = (lo >> 16) | (hi & 0xffff0000u);
+            uint32_t* out = (uint32_t*)s_raw + rg7 * (RAW_S / 2) + cp;
+            const uint16_t* va = s_v + rg7 * PW + ia;
+            const uint16_t* vb = s_v + rg7 * PW + ib;
+#pragma unroll kResizeUnroll
+            for (int k = 0; k < (RAW_H + 6) / 7; ++k) {                    // 6 rows per thread, the last one partial
+                if (rg7 + 7 * k < RAW_H) {
+                    const uint32_t lo = (uint32_t)va[7 * k * PW] * wa + (uint32_t)va[7 * k * PW + 1] * aa + 32768u;
+                    const uint32_t hi = (uint32_t)vb[7 * k * PW] * wb + (uint32_t)vb[7 * k * PW + 1] * ab + 32768u;
+                    out[7 * k * (RAW_S / 2)] = (lo >> 16) | (hi & 0xffff0000u);
+                }
             }
         }
     }
@@ -621,7 +690,8 @@ int vs_configure_level_smem(const VsPlan& p)
     VS_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) dev = 0;
     if ((int)dyn > __atomic_load_n(&cur[dev], __ATOMIC_ACQUIRE)) {
-        VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        VS_CUDA(cudaFuncSetAttribute(vs_level_kernel<false, VS_PAR_W_STD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
         __atomic_store_n(&cur[dev], (int)dyn, __ATOMIC_RELEASE);
     }
     return VSLAM_OK;
@@ -676,7 +746,11 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
         CUtensorMap tm;
         memset(&tm, 0, sizeof(tm));
         int use_tma = 0;
-        if (l == 1)
+        if (l == 0)       // frames of at least one tile's halo in each direction (smaller ones reflect more than once)
+            use_tma = p.width >= 16 && p.height >= 16 &&
+                      vs_image_tensor_map(&tm, d_frames, p.width, p.height, (size_t)pitch, (size_t)pitch * p.height, batch,
+                                          L0_BOX_W, RAW_H);
+        else if (l == 1)
             use_tma = vs_image_tensor_map(&tm, d_frames, p.width, p.height, (size_t)pitch, (size_t)pitch * p.height, batch,
                                           p.par_w, p.par_h);
         else if (l > 1)
@@ -686,11 +760,14 @@ int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
         vs_prof_mark(o, l, s);
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         if (l == 0)
-            vs_level_kernel<true><<<grid, 256, 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
-                                                       o->d_cand, o->d_counters, tm, 0);
-        else
-            vs_level_kernel<false><<<grid, 256, dyn, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
+            vs_level_kernel<true, 0><<<grid, 256, 0, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
                                                           o->d_cand, o->d_counters, tm, use_tma);
+        else if (p.par_w == VS_PAR_W_STD && use_tma)
+            vs_level_kernel<false, VS_PAR_W_STD><<<grid, 256, dyn, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr,
+                                                                        o->d_tab, o->d_cand, o->d_counters, tm, use_tma);
+        else
+            vs_level_kernel<false, 0><<<grid, 256, dyn, s>>>(p, l, d_frames, pitch, (size_t)pitch * p.height, o->d_pyr, o->d_tab,
+                                                             o->d_cand, o->d_counters, tm, use_tma);
     }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;
