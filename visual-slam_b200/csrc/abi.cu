@@ -246,6 +246,8 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
     ALLOC(o->d_status, sizeof(int32_t));
     ALLOC(o->d_knn_idx, B * p.kp_cap * 2 * sizeof(int32_t));
     ALLOC(o->d_knn_dist, B * p.kp_cap * 2 * sizeof(int32_t));
+    o->knn_ws_bytes = B * vs_knn2_tc5_workspace_per_pair(p.kp_cap);
+    ALLOC(o->d_knn_ws, o->knn_ws_bytes);
 #undef ALLOC
     cudaError_t e = cudaMemcpy(o->d_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemset(o->d_status, 0, sizeof(int32_t));
@@ -269,7 +271,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     if (!o) return VSLAM_OK;
     cudaDeviceSynchronize();
     void* ptrs[] = {o->d_pyr, o->d_cand, o->d_stage, o->d_counters, o->d_tab, o->d_status, o->d_knn_idx,
-                    o->d_knn_dist, o->d_frames, o->d_bgr, o->d_track, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
+                    o->d_knn_dist, o->d_knn_ws, o->d_frames, o->d_bgr, o->d_track, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
     if (o->stream_in) cudaStreamDestroy(o->stream_in);

@@ -131,7 +131,7 @@ __global__ void vs_knn2_merge_kernel(const int4* __restrict__ partial, int nq_ma
 
 int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt, long t_stride,
                        const int32_t* d_nq, const int32_t* d_nt, int pairs, int nsplit, int4* partial,
-                       int32_t* d_idx, int32_t* d_dist, cudaStream_t s);
+                       int32_t* d_idx, int32_t* d_dist, uint8_t* ws, size_t ws_bytes, cudaStream_t s);
 
 // kNN-2 engines: tcgen05 kind::i8 (bf_match_tc5.cu) up to 65 536 train rows -- its keys pack the train index into
 // 16 bits -- and the XOR + POPC kernel above beyond.  VSLAM_KNN=popc forces the POPC kernel at every size: that is the
@@ -195,7 +195,9 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     vs_prof_mark(prof, VS_PROF_KNN2, s);
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (tc5) {
-        int rc = vs_knn2_tc5_launch(d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, pairs, nsplit, partial, d_idx, d_dist, s);
+        // a handle owns the expanded-tile workspace of its own batches (no allocation call on the hot path)
+        int rc = vs_knn2_tc5_launch(d_q, nq, q_stride, d_t, nt, t_stride, d_nq, d_nt, pairs, nsplit, partial, d_idx, d_dist,
+                                    prof ? prof->d_knn_ws : nullptr, prof ? prof->knn_ws_bytes : 0, s);
         if (rc) return rc;
     } else
         vs_knn2_kernel<<<dim3(qtiles, nsplit, pairs), BF_THREADS, 0, s>>>(

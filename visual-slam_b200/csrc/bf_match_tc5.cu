@@ -403,21 +403,29 @@ int vs_knn2_tc5_configure()
     return VSLAM_OK;
 }
 
+// bytes of expanded-tile workspace one descriptor pair with nt train rows needs
+size_t vs_knn2_tc5_workspace_per_pair(int nt) { return (size_t)((nt + T5_N - 1) / T5_N) * T5_TILE_BYTES; }
+
+// ws / ws_bytes: caller-owned workspace for the expanded train tiles (a handle's, sized at creation); when it is
+// missing or too small the tiles live in a stream-ordered allocation of this call
 int vs_knn2_tc5_launch(const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt, long t_stride,
                        const int32_t* d_nq, const int32_t* d_nt, int pairs, int nsplit, int4* partial,
-                       int32_t* d_idx, int32_t* d_dist, cudaStream_t s)
+                       int32_t* d_idx, int32_t* d_dist, uint8_t* ws, size_t ws_bytes, cudaStream_t s)
 {
     int rc = vs_knn2_tc5_configure();
     if (rc) return rc;
     const int tiles_max = (nt + T5_N - 1) / T5_N;
     uint8_t* expanded = nullptr;
+    bool own = false;
     if (tiles_max > 0) {                                           // an empty train set has nothing to expand
-        VS_CUDA(cudaMallocAsync((void**)&expanded, (size_t)pairs * tiles_max * T5_TILE_BYTES, s));
+        const size_t need = (size_t)pairs * tiles_max * T5_TILE_BYTES;
+        if (ws && ws_bytes >= need) expanded = ws;
+        else { VS_CUDA(cudaMallocAsync((void**)&expanded, need, s)); own = true; }
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);    // the caller counts the search kernel
         vs_knn2_expand_kernel<<<dim3(tiles_max, pairs), 512, 0, s>>>(d_t, nt, t_stride, d_nt, tiles_max, expanded);
     }
     vs_knn2_tc5_kernel<<<dim3((nq + T5_ROWS - 1) / T5_ROWS, nsplit, pairs), T5_THREADS, T5_DYN_SMEM, s>>>(
         d_q, nq, q_stride, expanded, tiles_max, nt, d_nq, d_nt, nsplit, partial, d_idx, d_dist);
-    if (expanded) VS_CUDA(cudaFreeAsync(expanded, s));
+    if (own) VS_CUDA(cudaFreeAsync(expanded, s));
     return VSLAM_OK;
 }

@@ -93,6 +93,8 @@ struct vslam_orb {
     // frontend scratch
     int32_t* d_knn_idx;    // [max_batch][kp_cap][2]
     int32_t* d_knn_dist;
+    uint8_t* d_knn_ws;     // expanded train tiles of the tcgen05 kNN-2: [max_batch] x vs_knn2_tc5_workspace_per_pair(kp_cap)
+    size_t knn_ws_bytes;   // bytes available from d_knn_ws (a chunk view of the handle sees its own slice)
     // host staging for *_host entry points
     uint8_t* d_frames;     // [max_batch][h][pitch0]
     uint8_t* d_track;      // outputs + workspace of vslam_track_clip_host (lazy, one block)
@@ -143,6 +145,7 @@ bool vs_image_tensor_map(struct CUtensorMap_st* tm, const uint8_t* base, int w, 
                          int frames, int box_w, int box_h);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
+size_t vs_knn2_tc5_workspace_per_pair(int nt);
 int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, const uint8_t* d_t, int nt,
                    long t_stride, const int32_t* d_nq, const int32_t* d_nt, int pairs,
                    int32_t* d_idx, int32_t* d_dist, cudaStream_t s);

@@ -533,7 +533,7 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
 {
     __shared__ __align__(128) uint8_t s_blur[8][TD_BLUR_BYTES];
     __shared__ __align__(128) uint8_t s_raw[8][2][TD_RAW_BYTES];
-    __shared__ __align__(8) unsigned long long s_bar[8][3];      // per warp: raw buffer 0 / 1, blurred window
+    __shared__ __align__(8) unsigned long long s_bar[8][4];      // per warp: raw buffer 0 / 1, blurred window A, blurred window B
     const int b = blockIdx.y, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int32_t* ctr = counters + (size_t)b * plan.n_levels * VS_CTR_STRIDE;
     __shared__ int s_start[VS_MAX_LEVELS + 1];
@@ -549,7 +549,7 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
     }
     const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[wid][0]);
     if (lane == 0) {
-        for (int k = 0; k < 3; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * k));
+        for (int k = 0; k < 4; ++k) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * k));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -664,11 +664,18 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
         sincos((double)rad, &sd, &cd);
         m_ca = (float)cd; m_sa = (float)sd;
     }
-    // Pass B: steered rBRIEF on the blurred window
+    // Pass B: steered rBRIEF on the blurred window.  Two window buffers per warp: A = s_blur[wid] (keypoint 0's window
+    // has been in flight since the start), B = the two unblurred-window buffers, which pass A no longer needs
+    // (2 x 1536 B >= 2432 B).  Keypoint k uses buffer k & 1 and, once its tests are done, hands the buffer to keypoint
+    // k + 2, so a window's TMA load flies while the previous keypoint's 256 tests run.
+    __syncwarp();
+    if (lane == 1 && lane < nk)
+        td_load(wr_u, &maps.blur[m_level], (m_cx - DESC_R) & ~15, m_cy - DESC_R, b, bar0 + 24, TD_BLUR_W * DESC_WIN);
     for (int k = 0; k < nk; ++k) {
         const float ca = __shfl_sync(0xffffffffu, m_ca, k), sa = __shfl_sync(0xffffffffu, m_sa, k);
         const int bx0 = __shfl_sync(0xffffffffu, m_cx, k) - DESC_R;           // first column of the window
-        td_wait(bar0 + 16, (uint32_t)k & 1u);
+        const uint8_t* win = (k & 1) ? &s_raw[wid][0][0] : wb;
+        td_wait(bar0 + 16 + 8 * (k & 1), (uint32_t)(k >> 1) & 1u);
         // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
         const float magic = 12582912.0f;
         const uint32_t off0 = (uint32_t)(DESC_R * TD_BLUR_W + DESC_R + (bx0 & 15)) - 0x4B400000u * (TD_BLUR_W + 1);
@@ -680,11 +687,12 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
             const float fx1 = __fsub_rn(__fmul_rn(p.z, ca), __fmul_rn(p.w, sa)), fy1 = __fadd_rn(__fmul_rn(p.z, sa), __fmul_rn(p.w, ca));
             const uint32_t i0w = __float_as_uint(__fadd_rn(fy0, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
             const uint32_t i1w = __float_as_uint(__fadd_rn(fy1, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
-            byte |= (uint32_t)(wb[i0w] < wb[i1w]) << t;
+            byte |= (uint32_t)(win[i0w] < win[i1w]) << t;
         }
         __syncwarp();
-        if (lane == k + 1 && lane < nk)
-            td_load(wb_u, &maps.blur[m_level], (m_cx - DESC_R) & ~15, m_cy - DESC_R, b, bar0 + 16, TD_BLUR_W * DESC_WIN);
+        if (lane == k + 2 && lane < nk)
+            td_load((k & 1) ? wr_u : wb_u, &maps.blur[m_level], (m_cx - DESC_R) & ~15, m_cy - DESC_R, b, bar0 + 16 + 8 * (k & 1),
+                    TD_BLUR_W * DESC_WIN);
         desc_out[((size_t)b * plan.kp_cap + i0 + k) * 32 + lane] = (uint8_t)byte;
     }
 }
