@@ -120,6 +120,42 @@ int vslam_undistort(const uint8_t* d_src, int batch, int height, int width, int 
                     uint8_t* d_dst, int pitch_dst, void* stream);
 int vslam_undistort_host(const uint8_t* h_src, int height, int width, int channels,
                          const double* h_K, const double* h_dist, int n_dist, uint8_t* h_dst);
+/* Video ingest on the device.  Replaces cv2.VideoCapture(path).read() + the extractor's
+ * cvtColor(BGR2GRAY) (src/tests/tester_map.py:58-66, run_video.py:138-149, extractor.py:61-62) for the DECODE and
+ * COLOUR part: compressed packets go to the GPU's NVDEC engine through libnvcuvid (dlopen'ed; the driver ships it)
+ * and come out as frames in HBM in the form the extractor takes.  The container is still demuxed on the host
+ * (cv2.VideoCapture in raw mode hands out the packets: orbslam2/ingest.py).  8-bit 4:2:0 streams.
+ *   vslam_nvdec_available   1 when libnvcuvid is loadable, else 0 (then vslam_nvdec_create fails with VSLAM_E_CUDA).
+ *   vslam_nvdec_decode      feeds one packet (h_packet may be NULL with bytes 0 and end_of_stream 1 to flush) and
+ *                           writes the frames that become displayable, in display order, to d_out + i * frame_stride
+ *                           (i < max_frames; *n_frames = how many; more than max_frames -> VSLAM_E_CAPACITY).
+ *                           mode VSLAM_NVDEC_LUMA: the Y plane; VSLAM_NVDEC_GRAY: the reference's gray bit for bit
+ *                           (swscale yuv420p -> bgr24, then OpenCV's BGR2GRAY); VSLAM_NVDEC_BGR: that BGR frame
+ *                           (uint8 [h][w][3], what cv2.VideoCapture.read() returns).  The frames are complete when
+ *                           the call returns (the decoder's surface is released at unmap).
+ *   vslam_nvdec_set_colour  the 16-bit fixed-point constants of swscale's conversion (defaults: ITU-R BT.601
+ *                           limited range, what cv2's FFmpeg backend selects). */
+#define VSLAM_CODEC_MPEG4 1
+#define VSLAM_CODEC_H264 2
+#define VSLAM_CODEC_MJPEG 3
+#define VSLAM_CODEC_HEVC 4
+#define VSLAM_CODEC_VP8 5
+#define VSLAM_CODEC_VP9 6
+#define VSLAM_CODEC_AV1 7
+#define VSLAM_NVDEC_LUMA 0
+#define VSLAM_NVDEC_GRAY 1
+#define VSLAM_NVDEC_BGR 2
+#define VSLAM_NVDEC_NV12 3   /* the decoder's surface as is: uint8 [h + h/2][w], luma rows then interleaved U, V rows */
+typedef struct vslam_nvdec vslam_nvdec;
+int vslam_nvdec_available(void);
+int vslam_nvdec_create(int codec, vslam_nvdec** out);
+int vslam_nvdec_destroy(vslam_nvdec* dec);
+int vslam_nvdec_set_colour(vslam_nvdec* dec, int cy, int cbu, int cgu, int cgv, int crv, int y_offset);
+int vslam_nvdec_frame_size(const vslam_nvdec* dec, int* width, int* height);
+int vslam_nvdec_decode(vslam_nvdec* dec, const uint8_t* h_packet, size_t bytes, int end_of_stream, int mode,
+                       uint8_t* d_out, int out_pitch, size_t frame_stride, int max_frames, int* n_frames,
+                       void* stream);
+
 /* cv2.cvtColor(COLOR_BGR2GRAY) on device buffers (d_bgr uint8 [n_pixels][3] -> d_gray uint8
  * [n_pixels]); bit-exact with OpenCV's fixed-point formula. */
 int vslam_bgr2gray(const uint8_t* d_bgr, size_t n_pixels, uint8_t* d_gray, void* stream);
