@@ -1,5 +1,5 @@
 """GPU-box probe for the NVDEC ingest: writes a short VP9 clip with cv2, decodes it (i) with cv2 on the CPU and
-(ii) with orbslam2.ingest.VideoReader on NVDEC, and compares / dumps what tools/fit_swscale.py needs."""
+(ii) with orbslam2.ingest.VideoReader on NVDEC, compares them and dumps (NV12, BGR) pairs for fitting the swscale constants."""
 import os
 import sys
 

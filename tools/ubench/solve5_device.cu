@@ -57,6 +57,10 @@ int main(int argc, char** argv)
         bool same = n == hn[i];
         for (int q = 0; same && q < n; ++q) same = fabs(out[q][0] - hE[(i * 10 + q) * 9]) < 1e-9;
         printf("sample %d: device %d host %d %s\n", i, hn[i], n, same ? "ok" : "MISMATCH");
+        if (!same && argc > 2) {
+            for (int q = 0; q < hn[i]; ++q) printf("   dev  %d: %.12f %.12f %.12f\n", q, hE[(i * 10 + q) * 9], hE[(i * 10 + q) * 9 + 1], hE[(i * 10 + q) * 9 + 2]);
+            for (int q = 0; q < n; ++q) printf("   host %d: %.12f %.12f %.12f\n", q, out[q][0], out[q][1], out[q][2]);
+        }
         bad += !same;
     }
     printf("%d of %d samples differ\n", bad, nsamp);

@@ -270,11 +270,16 @@ VS_HD VS_NOINLINE double polish_5pt(const double L[9][4], double c[4], double* s
 // leading coefficients vanished (roots at infinity of this chart), or the number of solutions found is odd.  (A start
 // value far from its solution is NOT a trigger: on a panning camera the elimination loses digits on every second
 // sample, the polish recovers them, and nothing is missed.)
-VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int n, bool* trouble)
+// The three stages of a pass, separately callable so that a kernel can give the (independent) polishes of a round's
+// roots to different threads (geom_track.cu); solve_5pt_in_basis below is their serial composition.  Stages 1 and 2
+// are NOT inlined on the device: cicc 12.9 overlays the local arrays of inlined callees on live arrays of the caller
+// at -O1 and above (see polish_5pt) -- with these two inlined, the first solution of every sample came back wrong.
+// tools/ubench/solve5_device.cu compares the device build with the host build of this very source.
+//
+// Stage 1: elimination in the basis nb -> L (entry e = 3i + j of E as a linear form in the basis coordinates) and one
+// unit start vector per real root of the degree-10 polynomial; returns the number of starts.
+VS_HD VS_NOINLINE int five_pt_starts(const double nb[4][9], double L[9][4], double starts[10][4], bool* deflated)
 {
-    const int have_before = n;
-    // entry e = 3*i + j of E as a linear form in (x, y, z, 1)
-    double L[9][4];
     for (int e = 0; e < 9; ++e)
         for (int k = 0; k < 4; ++k) L[e][k] = nb[k][e];
 
@@ -362,17 +367,13 @@ VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int 
         for (int i = 0; i <= 10; ++i) det[i] += prod[i];
     }
     double zs[10];
-    bool deflated = false;
-    const int nz = real_roots_deg10(det, zs, &deflated);
-    if (deflated) *trouble = true;
+    const int nz = real_roots_deg10(det, zs, deflated);
 #ifdef VS_5PT_TRACE
     VS_5PT_TRACE(det, zs, nz);
 #endif
+    int ns = 0;
     for (int s = 0; s < nz; ++s) {
         const double z = zs[s];
-#ifdef VS_5PT_TRACE2
-        VS_5PT_TRACE2(s, nz, z);
-#endif
         double b[3][3];
         for (int r = 0; r < 3; ++r)
             for (int c = 0; c < 3; ++c) {
@@ -392,39 +393,94 @@ VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int 
             }
         }
         if (bestD == 0.0 || !isfinite(x) || !isfinite(y)) continue;
-        double cc[4] = {x, y, z, 1.0};
-        {
-            const double cn = 1.0 / sqrt(x * x + y * y + z * z + 1.0);
-            for (int k = 0; k < 4; ++k) cc[k] *= cn;
-        }
-        double r_start;
-        const double r_end = polish_5pt(L, cc, &r_start);
-        if (!(r_end < 1e-16)) { *trouble = true; continue; }       // not a solution of the constraints
-        double Ek[9], nrm = 0.0;
+        const double cn = 1.0 / sqrt(x * x + y * y + z * z + 1.0);
+        starts[ns][0] = x * cn; starts[ns][1] = y * cn; starts[ns][2] = z * cn; starts[ns][3] = cn;
+        ++ns;
+    }
+    return ns;
+}
+
+// Stage 2: polish one start; on success Ek = the solution as a unit-Frobenius-norm matrix (singular values
+// (1/sqrt2, 1/sqrt2, 0), as cv2 returns it).  Returns 1 = solution, 0 = not a solution of the constraints
+// (the pass is then "in trouble"), -1 = degenerate, skip silently.
+VS_HD VS_NOINLINE int five_pt_finish(const double L[9][4], const double start[4], double Ek[9])
+{
+    double cc[4] = {start[0], start[1], start[2], start[3]};
+    double r_start;
+    const double r_end = polish_5pt(L, cc, &r_start);
+    if (!(r_end < 1e-16)) return 0;
+    double nrm = 0.0;
+    for (int e = 0; e < 9; ++e) {
+        Ek[e] = cc[0] * L[e][0] + cc[1] * L[e][1] + cc[2] * L[e][2] + cc[3] * L[e][3];
+        nrm += Ek[e] * Ek[e];
+    }
+    if (!(nrm > 0.0) || !isfinite(nrm)) return -1;
+    nrm = 1.0 / sqrt(nrm);
+    for (int e = 0; e < 9; ++e) Ek[e] *= nrm;
+    return 1;
+}
+
+// Stage 3: append Ek to E[0..n) unless it is already there (up to sign).  Returns the new count; *dup says it was.
+VS_HD inline int five_pt_merge(double E[10][9], int n, const double Ek[9], bool* dup)
+{
+    *dup = false;
+    for (int j = 0; j < n && !*dup; ++j) {
+        double dp = 0.0, dm = 0.0;
         for (int e = 0; e < 9; ++e) {
-            Ek[e] = cc[0] * L[e][0] + cc[1] * L[e][1] + cc[2] * L[e][2] + cc[3] * L[e][3];
-            nrm += Ek[e] * Ek[e];
+            dp = fmax(dp, fabs(E[j][e] - Ek[e]));
+            dm = fmax(dm, fabs(E[j][e] + Ek[e]));
         }
-        if (!(nrm > 0.0) || !isfinite(nrm)) continue;
-        nrm = 1.0 / sqrt(nrm);               // Frobenius norm 1 => singular values (1/sqrt2, 1/sqrt2, 0), as cv2 returns
-        bool dup = false;
-        for (int j = 0; j < n && !dup; ++j) {
-            double dp = 0.0, dm = 0.0;
-            for (int e = 0; e < 9; ++e) {
-                dp = fmax(dp, fabs(E[j][e] - Ek[e] * nrm));
-                dm = fmax(dm, fabs(E[j][e] + Ek[e] * nrm));
-            }
-            dup = fmin(dp, dm) < 1e-7;
-        }
-        if (dup) { if (have_before <= 0) *trouble = true; continue; }
-        if (n >= 10) break;
-        for (int e = 0; e < 9; ++e) E[n][e] = Ek[e] * nrm;
-        ++n;
+        *dup = fmin(dp, dm) < 1e-7;
+    }
+    if (*dup || n >= 10) return n;
+    for (int e = 0; e < 9; ++e) E[n][e] = Ek[e];
+    return n + 1;
+}
+
+VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int n, bool* trouble)
+{
+    const int have_before = n;
+    double L[9][4], starts[10][4];
+    bool deflated = false;
+    const int ns = five_pt_starts(nb, L, starts, &deflated);
+    if (deflated) *trouble = true;
+    for (int s = 0; s < ns; ++s) {
+        double Ek[9];
+        const int ok = five_pt_finish(L, starts[s], Ek);
+        if (ok == 0) *trouble = true;
+        if (ok <= 0) continue;
+        bool dup;
+        n = five_pt_merge(E, n, Ek, &dup);
+        if (dup && have_before <= 0) *trouble = true;
     }
     // the degree-10 polynomial has real coefficients: its real roots come in an even number (with multiplicity).
     // An odd count of distinct solutions after the first pass means one was missed or two collapsed.
     if (have_before <= 0 && (n & 1)) *trouble = true;
     return n;
+}
+
+// the fixed orthogonal mix of the Gauss-Jordan null-space basis the first pass runs in (see solve_5pt)
+VS_HD inline void five_pt_rotate_basis(const double nb[4][9], double rb[4][9])
+{
+    for (int e = 0; e < 9; ++e) {
+        const double a = nb[0][e], b = nb[1][e], c = nb[2][e], d = nb[3][e];
+        rb[0][e] = 0.5 * (a + b + c + d);
+        rb[1][e] = 0.5 * (a - b + c - d);
+        rb[2][e] = 0.5 * (a + b - c - d);
+        rb[3][e] = 0.5 * (a - b - c + d);
+    }
+}
+
+VS_HD inline void five_pt_null_space(const double x1[5][2], const double x2[5][2], double nb[4][9])
+{
+    double A[5][9];
+    for (int i = 0; i < 5; ++i) {
+        const double u = x1[i][0], v = x1[i][1], up = x2[i][0], vp = x2[i][1];
+        A[i][0] = up * u; A[i][1] = up * v; A[i][2] = up;
+        A[i][3] = vp * u; A[i][4] = vp * v; A[i][5] = vp;
+        A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
+    }
+    null_space_9<5>(A, nb);
 }
 
 // 5-point solver.  x1, x2: 5 correspondences in normalised camera coordinates.
@@ -435,27 +491,13 @@ VS_HD inline int solve_5pt_in_basis(const double nb[4][9], double E[10][9], int 
 // 4 x 4 mix, so other coordinates play the role of z) contributes the solutions the first one missed.
 VS_HD inline int solve_5pt(const double x1[5][2], const double x2[5][2], double E[10][9])
 {
-    double A[5][9], nb[4][9];
-    for (int i = 0; i < 5; ++i) {
-        const double u = x1[i][0], v = x1[i][1], up = x2[i][0], vp = x2[i][1];
-        A[i][0] = up * u; A[i][1] = up * v; A[i][2] = up;
-        A[i][3] = vp * u; A[i][4] = vp * v; A[i][5] = vp;
-        A[i][6] = u; A[i][7] = v; A[i][8] = 1.0;
-    }
-    null_space_9<5>(A, nb);
+    double nb[4][9], rb[4][9];
+    five_pt_null_space(x1, x2, nb);
     // First pass in a rotated basis (a fixed orthogonal 4 x 4 mix of the Gauss-Jordan basis): the un-mixed basis is
     // aligned with the coordinate structure of the constraint rows, and for pure sideways motion (a panning camera)
     // that puts solutions at infinity of the (x, y, z, 1) chart on almost every second sample; mixed, that alignment
-    // is gone and the second pass -- in the un-mixed basis -- is needed for the rare clustered-root cases only
-    // (44 % -> see profiles/r2_ransac_agreement.txt of the samples of the synthetic pan clip needed two passes before).
-    double rb[4][9];
-    for (int e = 0; e < 9; ++e) {
-        const double a = nb[0][e], b = nb[1][e], c = nb[2][e], d = nb[3][e];
-        rb[0][e] = 0.5 * (a + b + c + d);
-        rb[1][e] = 0.5 * (a - b + c - d);
-        rb[2][e] = 0.5 * (a + b - c - d);
-        rb[3][e] = 0.5 * (a - b - c + d);
-    }
+    // is gone and the second pass -- in the un-mixed basis -- is needed for the rare clustered-root cases only.
+    five_pt_rotate_basis(nb, rb);
     bool trouble = false;
     int n = solve_5pt_in_basis(rb, E, 0, &trouble);
     if (trouble) {

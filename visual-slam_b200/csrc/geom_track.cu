@@ -54,7 +54,9 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
                         double* __restrict__ out_t, int32_t* __restrict__ out_status)
 {
     __shared__ double s_models[TK_R * 10 * 9];
-    __shared__ int s_nm[TK_R], s_counts[TK_R * 10], s_idx[TK_R * 5];
+    __shared__ int s_nm[TK_R], s_counts[TK_R * 10], s_idx[TK_R * 5], s_ns[TK_R], s_trouble[TK_R];
+    __shared__ signed char s_ok[TK_R * 10];
+    __shared__ double s_basis[TK_R * 36];            // per sample: E's entries as linear forms in the pass's basis
     __shared__ unsigned long long s_rng_cursor;
     __shared__ int s_fail;
     __shared__ double s_best[9], s_R1[9], s_R2[9], s_t[3];
@@ -169,9 +171,15 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
         // the round's subsets from OpenCV's stream (EMEstimatorCallback has no checkSubset), drawn by warp 0
         if (wid == 0) cv_sample_round<5, false>(&s_rng_cursor, salt, n2, r0, R, s_idx, &s_fail, nullptr, nullptr, 10000);
         __syncthreads();
+        // The five-point solver in three stages (geom_5pt.cuh).  Stage 1 -- elimination to the degree-10 polynomial,
+        // its real roots, one start vector per root -- is one long serial chain per sample: lanes of warp 0.
+        // Stage 2 -- Gauss-Newton polish of every root on the cubic constraints -- is independent per (sample, root)
+        // and goes to the whole CTA (it was the other half of that chain while three warps waited at the barrier).
+        // Stage 3 -- de-duplication, the "was a root missed" tests and, rarely, the second pass -- back on warp 0.
         if (tid < R) {
             const int j = tid, it = r0 + j;
-            int ne = 0;
+            int ns = 0;
+            s_trouble[j] = 0;
             if (it < P.max_iters && it < s_fail) {
                 const int* idx = s_idx + j * 5;
                 double x1[5][2], x2[5][2];
@@ -179,12 +187,60 @@ vs_track_batched_kernel(const vslam_keypoint* __restrict__ kp_q, const vslam_key
                     const double2 a = p1[idx[k]], b = p2[idx[k]];
                     x1[k][0] = a.x; x1[k][1] = a.y; x2[k][0] = b.x; x2[k][1] = b.y;
                 }
-                double E[10][9];
-                ne = solve_5pt(x1, x2, E);
-                for (int k = 0; k < ne; ++k)
-                    for (int e = 0; e < 9; ++e) s_models[(j * 10 + k) * 9 + e] = E[k][e];
+                double nb[4][9], rb[4][9], L[9][4], starts[10][4];
+                five_pt_null_space(x1, x2, nb);
+                five_pt_rotate_basis(nb, rb);
+                bool deflated = false;
+                ns = five_pt_starts(rb, L, starts, &deflated);
+                if (deflated) s_trouble[j] = 1;
+                for (int e = 0; e < 36; ++e) s_basis[j * 36 + e] = (&L[0][0])[e];
+                for (int k = 0; k < ns; ++k)
+                    for (int e = 0; e < 4; ++e) s_models[(j * 10 + k) * 9 + e] = starts[k][e];
             }
-            s_nm[j] = ne;
+            s_ns[j] = ns;
+        }
+        __syncthreads();
+        for (int t = tid; t < R * 10; t += TK_THREADS) {
+            const int j = t / 10, k = t - 10 * j;
+            if (k >= s_ns[j]) continue;
+            double* slot = s_models + t * 9;
+            const double st[4] = {slot[0], slot[1], slot[2], slot[3]};
+            double Ek[9];
+            const int ok = five_pt_finish((const double(*)[4])(s_basis + j * 36), st, Ek);
+            if (ok > 0)
+                for (int e = 0; e < 9; ++e) slot[e] = Ek[e];
+            s_ok[t] = ok;
+        }
+        __syncthreads();
+        if (tid < R) {
+            const int j = tid, ns = s_ns[j];
+            double (*Ej)[9] = (double(*)[9])(s_models + j * 90);
+            bool trouble = s_trouble[j] != 0;
+            int n = 0;
+            for (int k = 0; k < ns; ++k) {
+                const int ok = s_ok[j * 10 + k];
+                if (ok == 0) trouble = true;
+                if (ok <= 0) continue;
+                double Ek[9];
+                for (int e = 0; e < 9; ++e) Ek[e] = Ej[k][e];
+                bool dup;
+                n = five_pt_merge(Ej, n, Ek, &dup);           // in place: slot n <= k has been read already
+                if (dup) trouble = true;
+            }
+            if (n & 1) trouble = true;
+            if (trouble && ns + (int)s_trouble[j] > 0) {      // second pass in the un-mixed basis (rare), serial
+                const int* idx = s_idx + j * 5;
+                double x1[5][2], x2[5][2];
+                for (int k = 0; k < 5; ++k) {
+                    const double2 a = p1[idx[k]], b = p2[idx[k]];
+                    x1[k][0] = a.x; x1[k][1] = a.y; x2[k][0] = b.x; x2[k][1] = b.y;
+                }
+                double nb[4][9];
+                five_pt_null_space(x1, x2, nb);
+                bool t2 = false;
+                n = solve_5pt_in_basis(nb, Ej, n, &t2);
+            }
+            s_nm[j] = n;
         }
         __syncthreads();
         for (int slot = wid; slot < R * 10; slot += TK_THREADS / 32) {

@@ -165,9 +165,10 @@ CuvidApi& cuvid()
 //     r  = y + mulhi16(V', crv);  each clamped to [0, 255]                          (paddsw + packuswb)
 // i.e. the SIMD path of libswscale/x86/yuv2rgb_template.c with the ITU-R BT.601 limited-range table that
 // sws_getCachedContext selects by default.  The five coefficients and the luma offset are host parameters of the
-// kernel (vslam_nvdec_set_colour), because they are what a different swscale build or colour space would change;
-// the defaults were fitted and then verified EXACTLY against cv2's BGR output on the GPU box
-// (tools/fit_swscale.py, tests/test_gpu_ingest.py).
+// kernel (vslam_nvdec_set_colour), because they are what a different swscale build or colour space would change.
+// UNVERIFIED: the defaults are the textbook 13-bit BT.601 values; they were to be fitted against cv2's BGR output on a
+// box with NVDEC, and this pool's boxes do not expose the engine (profiles/r2_nvdec_probe.txt).
+// tests/test_gpu_ingest.py holds the bit-equality check for the day it runs on one that does.
 struct VsYuvCoef { int cy, cbu, cgu, cgv, crv, yoff; };
 
 __device__ __forceinline__ int mulhi16(int a, int b) { return (a * b) >> 16; }     // pmulhw on sign-extended lanes
