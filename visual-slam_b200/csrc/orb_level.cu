@@ -92,12 +92,16 @@ __device__ __forceinline__ int smem_atomic_add(int* p, int v)
 // values above cen + thr, or both below cen - thr.  Returns bit 15 / 31 set for the lanes that pass.  (The weaker
 // "second-largest above / second-smallest below" test of round 1 queued 28 % of the pairs of the bench clip; the
 // networks and the NMS walk run on the queue only.)
-__device__ __forceinline__ uint32_t compass_need(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t cen, uint32_t kbias)
+__device__ __forceinline__ uint32_t compass_need(uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t cen, uint32_t kbias15)
 {
-    const uint32_t hi = __vimax3_u16x2(__vminu2(a, c), __vminu2(c, b), __vmaxu2(__vminu2(b, d), __vminu2(d, a)));   // brightest adjacent pair
-    const uint32_t lo = __vimin3_u16x2(__vmaxu2(a, c), __vmaxu2(c, b), __vminu2(__vmaxu2(b, d), __vmaxu2(d, a)));   // darkest adjacent pair
-    const uint32_t m = __vmaxu2((hi + kbias) - cen, (cen + kbias) - lo);   // max(hi - cen, cen - lo) - thr + 512
-    return ((m + 0x7fff7fffu) - 0x02000200u) & 0x80008000u;               // lanes with m > 512
+    // the ring is a - c - b - d - a: every adjacent pair takes one point of {a, b} and one of {c, d}, so "some
+    // adjacent pair is above T" <=> max(a, b) > T and max(c, d) > T, and likewise below
+    const uint32_t hi = __vminu2(__vmaxu2(a, b), __vmaxu2(c, d));     // brightest adjacent pair (its darker point)
+    const uint32_t lo = __vmaxu2(__vminu2(a, b), __vminu2(c, d));     // darkest adjacent pair (its brighter point)
+    // lanes biased by kbias15 = 0x7fff - thr: bit 15 of a lane <=> difference > thr.  Each lane sum stays inside
+    // [0x7f00 - thr, 0x80fe - thr], so the 32-bit adds are lane-wise adds
+    const uint32_t m = __vmaxu2(hi + kbias15 - cen, cen + kbias15 - lo);
+    return m & 0x80008000u;
 }
 
 // one pixel (ring columns of the tile); p points into the 16-bit tile
@@ -158,7 +162,7 @@ __device__ __forceinline__ uint32_t load4_edge(const uint8_t* row, int gx, int W
 // Row pass of the 7-tap Gaussian for 8 adjacent pixels: q = 8 words of the 16-bit tile starting 4
 // columns left of the first pixel, dst = 8 floats.  cv2 order: k0*x0, then one tap at a time.
 template <bool FMA>
-__device__ __forceinline__ void blur_row_item(const uint2* q, float* dst)
+__device__ __forceinline__ void blur_row_item(const uint2* q, float* dst0, float* dst1)
 {
     const float k0 = __uint_as_float(c_gauss_bits[0]), k1 = __uint_as_float(c_gauss_bits[1]),
                 k2 = __uint_as_float(c_gauss_bits[2]), k3 = __uint_as_float(c_gauss_bits[3]);
@@ -182,8 +186,8 @@ __device__ __forceinline__ void blur_row_item(const uint2* q, float* dst)
         }
         o[j] = s;
     }
-    *(float4*)dst = make_float4(o[0], o[1], o[2], o[3]);
-    *(float4*)(dst + 4) = make_float4(o[4], o[5], o[6], o[7]);
+    *(float4*)dst0 = make_float4(o[0], o[1], o[2], o[3]);
+    *(float4*)dst1 = make_float4(o[4], o[5], o[6], o[7]);
 }
 
 // Column pass for 4 columns x 2 output rows: p = row-pass results of the first output row's
@@ -244,7 +248,8 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __shared__ __align__(16) uint16_t s_raw_store[RAW_H * RAW_S + 8];
     uint16_t* const s_raw = s_raw_store + 8;
     __shared__ uint16_t s_queue[SC_H * (VS_TW / 2 + 2)];   // (row << 6) | word of the pixel pairs that pass the pre-test
-    __shared__ int s_nq;
+    __shared__ uint16_t s_queue2[SC_H * (VS_TW / 2)];      // the queued pairs that hold a score and can hold a kept corner
+    __shared__ int s_nq, s_nq2;
     __shared__ __align__(16) uint16_t s_sc[SC_H * SC_S];   // max(S - thr, 0), 16-bit lanes
     __shared__ __align__(16) float s_row[BL_ROWS * VS_TW];
     __shared__ uint32_t s_hist[256];
@@ -262,7 +267,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     uint8_t* fpyr = pyr + (size_t)b * plan.pyr_frame_bytes;
 
     s_hist[tid] = 0;
-    if (tid == 0) { s_nq = 0; s_n = 0; }
+    if (tid == 0) { s_nq = 0; s_nq2 = 0; s_n = 0; }
 
     // ---- 1. raw tile (16-bit lanes) ------------------------------------------
     if (L0 && use_tma) {
@@ -291,25 +296,29 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 "D%=:\n}\n" ::"r"(bar) : "memory");
         }
         const int wd = tid % (RAW_W / 4), rg = tid / (RAW_W / 4);        // 18 word columns x 14 row groups
-        const bool interior = x0 >= VS_HALO && x0 + VS_TW + VS_HALO <= W && y0 >= VS_HALO && y0 + VS_TH + VS_HALO <= H;
+        const int gx = x0 - VS_HALO + 4 * wd;
+        const bool yin = y0 >= VS_HALO && y0 + VS_TH + VS_HALO <= H;    // no mirrored rows in this tile
+        const bool xin = gx >= 0 && gx + 3 < W;                          // this word lies inside the frame's columns
+        const bool xleft = gx == -VS_HALO && W >= 8;                     // columns -4 .. -1 = columns 4, 3, 2, 1
         if (rg < 14) {
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const int r = rg + 14 * k;
                 if (r < RAW_H) {
+                    // mirrored row, clamped into the box where the pixel cannot matter (beyond the halo)
+                    int br = r;
+                    if (!yin) br = min(max((H - 1) - abs((H - 1) - abs(y0 - VS_HALO + r)) - (y0 - VS_HALO), 0), RAW_H - 1);
+                    const uint8_t* row = s_box + br * L0_BOX_W;
                     uint32_t u;
-                    if (interior) {
-                        u = *(const uint32_t*)(s_box + r * L0_BOX_W + 12 + 4 * wd);
+                    if (xin) {
+                        u = *(const uint32_t*)(row + 12 + 4 * wd);
+                    } else if (xleft) {
+                        u = __byte_perm(*(const uint32_t*)(row + 16), *(const uint32_t*)(row + 20), 0x1234);
                     } else {
-                        // mirrored row / columns, clamped into the box where the pixel cannot matter (beyond the halo)
-                        const int gy = y0 - VS_HALO + r;
-                        const int br = min(max((H - 1) - abs((H - 1) - abs(gy)) - (y0 - VS_HALO), 0), RAW_H - 1);
-                        const uint8_t* row = s_box + br * L0_BOX_W;
                         u = 0;
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            const int gx = x0 - VS_HALO + 4 * wd + j;
-                            const int bc = min(max((W - 1) - abs((W - 1) - abs(gx)) - (x0 - 16), 0), L0_BOX_W - 1);
+                            const int bc = min(max((W - 1) - abs((W - 1) - abs(gx + j)) - (x0 - 16), 0), L0_BOX_W - 1);
                             u |= (uint32_t)row[bc] << (8 * j);
                         }
                     }
@@ -502,6 +511,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     // (columns 30 .. W-31, rows 30 .. H-31); everything else stays 0.
     const int thr = plan.fast_thr;
     const uint32_t kbias = (uint32_t)(512 - thr) * 0x00010001u;
+    const uint32_t kbias15 = (uint32_t)(0x7fff - thr) * 0x00010001u;
     const int cx_lo = VS_EDGE - 1, cx_hi = W - VS_EDGE, cy_lo = VS_EDGE - 1, cy_hi = H - VS_EDGE;
     const int lane = tid & 31;
     // 3a. compass pre-test.  Any arc of 9 contains at least two of the four compass points, so a corner
@@ -521,8 +531,8 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 const uint2 up = *(const uint2*)(base + 3 * RAW_S + 4), dn = *(const uint2*)(base - 3 * RAW_S + 4);
                 const uint2* q = (const uint2*)base;
                 const uint2 a = q[0], m = q[1], e = q[2];
-                need[2 * k] = compass_need(up.x, dn.x, fsr16(m.y, e.x), fsr16(a.x, a.y), m.x, kbias);
-                need[2 * k + 1] = compass_need(up.y, dn.y, fsr16(e.x, e.y), fsr16(a.y, m.x), m.y, kbias);
+                need[2 * k] = compass_need(up.x, dn.x, fsr16(m.y, e.x), fsr16(a.x, a.y), m.x, kbias15);
+                need[2 * k + 1] = compass_need(up.y, dn.y, fsr16(e.x, e.y), fsr16(a.y, m.x), m.y, kbias15);
             }
             *(uint2*)(s_sc + r * SC_S + 4 + 4 * w) = make_uint2(0u, 0u);
         }
@@ -556,7 +566,7 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         if (gy >= cy_lo && gy <= cy_hi && gx >= cx_lo && gx <= cx_hi) {
             const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
             const uint32_t need = compass_need(rw[3 * (RAW_S / 2)], rw[-3 * (RAW_S / 2)], fsr16(rw[1], rw[2]), fsr16(rw[-2], rw[-1]),
-                                               rw[0], kbias) & (side ? 0x00008000u : 0x80000000u);
+                                               rw[0], kbias15) & (side ? 0x00008000u : 0x80000000u);
             if (need) s_queue[smem_atomic_add(&s_nq, 1)] = (uint16_t)((r << 6) | wi);
         }
         ((uint32_t*)(s_sc + r * SC_S))[wi] = 0u;
@@ -566,59 +576,82 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     // cv2's vector blocks use FMA, its scalar tails do not: rows switch at W - W%32,
     // columns at W - W%8; an aligned 8-pixel group never straddles either boundary.
     const int wrow = W & ~31, wcol = W & ~7;
-    for (int i = tid; i < BL_ROWS * (VS_TW / 8); i += 256) {
+    auto row_item = [&](int i) {
         const int g = i & 7, rr = i >> 3;                             // s_row row rr <-> gy = y0 - 3 + rr
-        if (y0 - 3 + rr >= H + 3) continue;                           // below every output row of the level
+        if (y0 - 3 + rr >= H + 3) return;                             // below every output row of the level
         const uint2* q = (const uint2*)(s_raw + (rr + 1) * RAW_S + 8 * g);
-        float* dst = s_row + rr * VS_TW + 8 * g;
-        if (x0 + 8 * g < wrow) blur_row_item<true>(q, dst);
-        else blur_row_item<false>(q, dst);
-    }
+        // 4-float chunk c of a row sits at chunk position c ^ (c >> 3): the eight lanes of a store phase (g = 0..7,
+        // chunks 2g) then cover all 32 banks instead of colliding pairwise (g, g + 4); the column pass reads chunk w
+        // of 16 neighbouring lanes at w ^ (w >> 3), still conflict-free
+        float* dst = s_row + rr * VS_TW;
+        const int sw = g >> 2;
+        if (x0 + 8 * g < wrow) blur_row_item<true>(q, dst + 4 * ((2 * g) ^ sw), dst + 4 * ((2 * g + 1) ^ sw));
+        else blur_row_item<false>(q, dst + 4 * ((2 * g) ^ sw), dst + 4 * ((2 * g + 1) ^ sw));
+    };
+    // 288 items: one per thread here; the last 32 (rows 32 .. 35) run on the last warp in the NMS interval, where
+    // only the one or two warps that hold scored pairs have work -- a second pass here would keep seven warps
+    // waiting at the barrier for the one that has it
+    row_item(tid);
     __syncthreads();
 
-    // ---- 3b. exact scores of the queued pairs: word wi of score row r <-> tile columns 2wi, 2wi+1
+    // ---- 3b. exact scores of the queued pairs: word wi of score row r <-> tile columns 2wi, 2wi+1.  Pairs that
+    // hold a score and can hold a kept corner (not the ring, rows inside the 31-px border) go to a second queue:
+    // the NMS pass then runs on whole warps of scored pairs instead of walking the first queue with most lanes idle.
     {
         const int nqueue = s_nq;
-        for (int qi = tid; qi < nqueue; qi += 256) {
-            const int e = s_queue[qi], r = e >> 6, wi = e & 63;
-            const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
-            const int RW = RAW_S / 2;
-            uint32_t v[16];
-            {
-                const uint32_t m1 = rw[3 * RW - 1], z = rw[3 * RW], p1 = rw[3 * RW + 1];
-                v[0] = z; v[1] = fsr16(z, p1); v[15] = fsr16(m1, z);
+        const int cyk_lo = max(VS_EDGE - (y0 - 1), 1), cyk_hi = min(H - VS_EDGE - (y0 - 1), SC_H - 1);   // kept score rows [lo, hi)
+        for (int q0 = tid & ~31; q0 < nqueue; q0 += 256) {              // warp-uniform trip count (ballot below)
+            const int qi = q0 + lane;
+            bool keep = false;
+            int e = 0;
+            if (qi < nqueue) {
+                e = s_queue[qi];
+                const int r = e >> 6, wi = e & 63;
+                const uint32_t* rw = (const uint32_t*)(s_raw + (r + 3) * RAW_S) + wi;
+                const int RW = RAW_S / 2;
+                uint32_t v[16];
+                {
+                    const uint32_t m1 = rw[3 * RW - 1], z = rw[3 * RW], p1 = rw[3 * RW + 1];
+                    v[0] = z; v[1] = fsr16(z, p1); v[15] = fsr16(m1, z);
+                }
+                {
+                    const uint32_t m1 = rw[-3 * RW - 1], z = rw[-3 * RW], p1 = rw[-3 * RW + 1];
+                    v[8] = z; v[7] = fsr16(z, p1); v[9] = fsr16(m1, z);
+                }
+                v[2] = rw[2 * RW + 1]; v[14] = rw[2 * RW - 1];
+                v[6] = rw[-2 * RW + 1]; v[10] = rw[-2 * RW - 1];
+                v[3] = fsr16(rw[RW + 1], rw[RW + 2]); v[13] = fsr16(rw[RW - 2], rw[RW - 1]);
+                v[5] = fsr16(rw[-RW + 1], rw[-RW + 2]); v[11] = fsr16(rw[-RW - 2], rw[-RW - 1]);
+                v[4] = fsr16(rw[1], rw[2]); v[12] = fsr16(rw[-2], rw[-1]);
+                uint32_t o = fast_pair(v, rw[0], kbias);
+                const int gx = x0 - VS_HALO + 2 * wi;
+                if (gx < cx_lo || gx > cx_hi) o &= 0xffff0000u;
+                if (gx + 1 < cx_lo || gx + 1 > cx_hi) o &= 0x0000ffffu;
+                ((uint32_t*)(s_sc + r * SC_S))[wi] = o;
+                keep = o != 0 && r >= cyk_lo && r < cyk_hi && wi >= 2 && wi <= VS_TW / 2 + 1;
             }
-            {
-                const uint32_t m1 = rw[-3 * RW - 1], z = rw[-3 * RW], p1 = rw[-3 * RW + 1];
-                v[8] = z; v[7] = fsr16(z, p1); v[9] = fsr16(m1, z);
+            const uint32_t km = __ballot_sync(0xffffffffu, keep);
+            if (km) {
+                int base = 0;
+                if (lane == 0) base = smem_atomic_add(&s_nq2, __popc(km));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (keep) s_queue2[base + __popc(km & ((1u << lane) - 1u))] = (uint16_t)e;
             }
-            v[2] = rw[2 * RW + 1]; v[14] = rw[2 * RW - 1];
-            v[6] = rw[-2 * RW + 1]; v[10] = rw[-2 * RW - 1];
-            v[3] = fsr16(rw[RW + 1], rw[RW + 2]); v[13] = fsr16(rw[RW - 2], rw[RW - 1]);
-            v[5] = fsr16(rw[-RW + 1], rw[-RW + 2]); v[11] = fsr16(rw[-RW - 2], rw[-RW - 1]);
-            v[4] = fsr16(rw[1], rw[2]); v[12] = fsr16(rw[-2], rw[-1]);
-            uint32_t o = fast_pair(v, rw[0], kbias);
-            const int gx = x0 - VS_HALO + 2 * wi;
-            if (gx < cx_lo || gx > cx_hi) o &= 0xffff0000u;
-            if (gx + 1 < cx_lo || gx + 1 > cx_hi) o &= 0x0000ffffu;
-            ((uint32_t*)(s_sc + r * SC_S))[wi] = o;
         }
     }
     __syncthreads();
 
+    if (tid >= 256 - (BL_ROWS * (VS_TW / 8) - 256)) row_item(tid + (BL_ROWS * (VS_TW / 8) - 256));   // the rest of 4a
+
     // ---- 5. non-max suppression (strict >, non-corners count as 0) + 31-px border -> tile list + histogram.
-    // Only queued pairs can hold a score, so the queue is walked again instead of the whole tile: word wi of
-    // score row r and its eight neighbouring words give the 3x3 neighbourhoods of both pixels at once.
+    // Word wi of score row r and its eight neighbouring words give the 3x3 neighbourhoods of both pixels at once.
     {
-        const int nqueue = s_nq;
-        for (int qi = tid; qi < nqueue; qi += 256) {
-            const int e = s_queue[qi], r = e >> 6, wi = e & 63;
-            if (r == 0 || r == SC_H - 1 || wi < 2 || wi > VS_TW / 2 + 1) continue;   // ring: neighbours only
+        const int nq2 = s_nq2;
+        for (int qi = tid; qi < nq2; qi += 256) {
+            const int e = s_queue2[qi], r = e >> 6, wi = e & 63;
             const uint32_t* q = (const uint32_t*)(s_sc + r * SC_S) + wi;
             const uint32_t cm = q[0];
-            if (cm == 0) continue;
             const int gy = y0 - 1 + r;
-            if (gy < VS_EDGE || gy >= H - VS_EDGE) continue;
             const int SW = SC_S / 2;
             const uint32_t ml = q[-1], mr = q[1], ul = q[-SW - 1], uc = q[-SW], ur = q[-SW + 1],
                            dl = q[SW - 1], dc = q[SW], dr = q[SW + 1];
@@ -660,8 +693,9 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
         const int gx = x0 + 4 * w, gy = y0 + ty;
         if (gx >= L.pitch || gy >= H) continue;
         uint32_t o0, o1;
-        if (gx < wcol) blur_col_item<true>(s_row + ty * VS_TW + 4 * w, o0, o1);
-        else blur_col_item<false>(s_row + ty * VS_TW + 4 * w, o0, o1);
+        const float* src = s_row + ty * VS_TW + 4 * (w ^ (w >> 3));
+        if (gx < wcol) blur_col_item<true>(src, o0, o1);
+        else blur_col_item<false>(src, o0, o1);
         uint8_t* dst = blur + (size_t)gy * L.pitch + gx;
         *(uint32_t*)dst = o0;
         if (gy + 1 < H) *(uint32_t*)(dst + L.pitch) = o1;

@@ -10,7 +10,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvslam_b200.so")
+# VSLAM_LIB_PATH: a differently built libvslam_b200 (kernel A/B runs, tools/build_variant.py); same ABI, same loud failure
+LIB_PATH = os.environ.get("VSLAM_LIB_PATH") or os.path.join(_HERE, "libvslam_b200.so")
 _LIB = None
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
