@@ -246,7 +246,7 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
     ALLOC(o->d_status, sizeof(int32_t));
     ALLOC(o->d_knn_idx, B * p.kp_cap * 2 * sizeof(int32_t));
     ALLOC(o->d_knn_dist, B * p.kp_cap * 2 * sizeof(int32_t));
-    o->knn_ws_bytes = B * vs_knn2_tc5_workspace_per_pair(p.kp_cap);
+    o->knn_ws_bytes = (B + 1) * vs_knn2_tc5_workspace_per_pair(p.kp_cap);   // + 1: a batch of one matched against the previous frame expands two sets
     ALLOC(o->d_knn_ws, o->knn_ws_bytes);
 #undef ALLOC
     cudaError_t e = cudaMemcpy(o->d_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);

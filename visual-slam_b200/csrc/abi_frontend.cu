@@ -166,7 +166,7 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
         view.d_knn_idx += f0 * cap * 2;
         view.d_knn_dist += f0 * cap * 2;
         view.d_knn_ws += f0 * vs_knn2_tc5_workspace_per_pair((int)cap);
-        view.knn_ws_bytes = (size_t)n * vs_knn2_tc5_workspace_per_pair((int)cap);
+        view.knn_ws_bytes = (size_t)(n + (nchunks == 1 ? 1 : 0)) * vs_knn2_tc5_workspace_per_pair((int)cap);   // chunks own disjoint slices
         view.knn_no_split = 1;
         rc = vslam_orb_detect_and_compute(&view, o->d_frames + f0 * fbytes, n, p.width, o->d_kp + f0 * cap,
                                           o->d_desc + f0 * cap * 32, o->d_count + f0, cs);

@@ -93,7 +93,7 @@ struct vslam_orb {
     // frontend scratch
     int32_t* d_knn_idx;    // [max_batch][kp_cap][2]
     int32_t* d_knn_dist;
-    uint8_t* d_knn_ws;     // expanded train tiles of the tcgen05 kNN-2: [max_batch] x vs_knn2_tc5_workspace_per_pair(kp_cap)
+    uint8_t* d_knn_ws;     // expanded descriptor tiles of the tcgen05 kNN-2: [max_batch + 1] x vs_knn2_tc5_workspace_per_pair(kp_cap)
     size_t knn_ws_bytes;   // bytes available from d_knn_ws (a chunk view of the handle sees its own slice)
     // host staging for *_host entry points
     uint8_t* d_frames;     // [max_batch][h][pitch0]
