@@ -142,7 +142,7 @@ int vs_configure_octree_smem(void);
 int vs_launch_octree(vslam_orb* o, int batch, cudaStream_t s);
 struct CUtensorMap_st;
 bool vs_image_tensor_map(struct CUtensorMap_st* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
-                         int frames, int box_w, int box_h);
+                         int frames, int box_w, int box_h, bool swizzle64 = false);
 int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                      vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count, cudaStream_t s);
 size_t vs_knn2_tc5_workspace_per_pair(int nt);

@@ -755,19 +755,22 @@ static vs_encode_tiled_fn vs_encode_tiled()
 
 // Tensor map of an image stack uint8 [frames][h][pitch] with a (box_w, box_h, 1) box.  Returns false when TMA
 // cannot describe it (unaligned base / strides, box too large); the kernels then stage by hand.  A box must start
-// on a 16-byte boundary of the innermost dimension (an unaligned x faults with "illegal instruction").
+// on a 16-byte boundary of the innermost dimension (an unaligned x faults with "illegal instruction").  swizzle64:
+// the box lands in shared memory with bits 4-5 of every byte address XORed with bits 7-8 (CU_TENSOR_MAP_SWIZZLE_64B).
 bool vs_image_tensor_map(struct CUtensorMap_st* tm, const uint8_t* base, int w, int h, size_t pitch, size_t frame_stride,
-                         int frames, int box_w, int box_h)
+                         int frames, int box_w, int box_h, bool swizzle64)
 {
     vs_encode_tiled_fn enc = vs_encode_tiled();
     if (!enc || box_w > 256 || box_h > 256 || (box_w & 15) || w <= 0 || h <= 0 || frames <= 0) return false;
+    if (swizzle64 && box_w != 64) return false;   // the box row is exactly one swizzle span
     if (((uintptr_t)base & 15) || (pitch & 15) || (frame_stride & 15)) return false;
     const cuuint64_t gdim[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
     const cuuint64_t gstr[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
     const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+               swizzle64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int vs_launch_levels(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch, cudaStream_t s)

@@ -503,6 +503,20 @@ vs_describe_kernel(const __grid_constant__ VsPlan plan, const uint8_t* __restric
 #define TD_RAW_W 48
 #define TD_RAW_BYTES 1536                 // 31 rows x 48 B = 1488, padded to the 128-byte TMA destination alignment
 #define TD_BLUR_W 64
+// The blurred window is 37 rows of 64 B, of which a keypoint's patch touches ~9 words per row: without a swizzle the
+// 512 byte gathers of a keypoint land on 18 of the 32 banks (bank = 16 (y & 1) + (x >> 2)) and cost 4.8 wavefronts
+// per warp load.  With the 64-byte TMA swizzle (address bits 4-5 ^= bits 7-8) the four 16-byte chunks of a row are
+// permuted differently in successive row pairs, the gathers spread over every bank, and the reader applies the same
+// XOR to its address.
+#ifndef VS_DESC_SWIZZLE
+#define VS_DESC_SWIZZLE 1
+#endif
+__device__ __forceinline__ uint32_t td_lds_u8_swz(uint32_t saddr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr ^ ((saddr >> 3) & 0x30u)));
+    return v;
+}
 #define TD_BLUR_BYTES 2432                // 37 rows x 64 B = 2368, padded likewise
 struct alignas(128) VsDescMaps {
     CUtensorMap raw[8], blur[8];          // per level; raw[0] is the caller's frame stack
@@ -675,6 +689,8 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
         const float ca = __shfl_sync(0xffffffffu, m_ca, k), sa = __shfl_sync(0xffffffffu, m_sa, k);
         const int bx0 = __shfl_sync(0xffffffffu, m_cx, k) - DESC_R;           // first column of the window
         const uint8_t* win = (k & 1) ? &s_raw[wid][0][0] : wb;
+        const uint32_t win_u = (k & 1) ? wr_u : wb_u;
+        (void)win; (void)win_u;
         td_wait(bar0 + 16 + 8 * (k & 1), (uint32_t)(k >> 1) & 1u);
         // cvRound(f) as the low mantissa bits of f + 1.5 * 2^23 (round half to even, |f| < 2^22)
         const float magic = 12582912.0f;
@@ -687,7 +703,11 @@ vs_describe_tma_kernel(const __grid_constant__ VsPlan plan, const __grid_constan
             const float fx1 = __fsub_rn(__fmul_rn(p.z, ca), __fmul_rn(p.w, sa)), fy1 = __fadd_rn(__fmul_rn(p.z, sa), __fmul_rn(p.w, ca));
             const uint32_t i0w = __float_as_uint(__fadd_rn(fy0, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx0, magic)) + off0;
             const uint32_t i1w = __float_as_uint(__fadd_rn(fy1, magic)) * TD_BLUR_W + __float_as_uint(__fadd_rn(fx1, magic)) + off0;
+#if VS_DESC_SWIZZLE
+            byte |= (uint32_t)(td_lds_u8_swz(win_u + i0w) < td_lds_u8_swz(win_u + i1w)) << t;
+#else
             byte |= (uint32_t)(win[i0w] < win[i1w]) << t;
+#endif
         }
         __syncwarp();
         if (lane == k + 2 && lane < nk)
@@ -745,7 +765,7 @@ int vs_launch_select(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch
                      : vs_image_tensor_map(&maps.raw[l], o->d_pyr + L.raw_off, L.w, L.h, (size_t)L.pitch, p.pyr_frame_bytes, batch,
                                            TD_RAW_W, IC_WIN);
         tma = tma && vs_image_tensor_map(&maps.blur[l], o->d_pyr + L.blur_off, L.w, L.h, (size_t)L.pitch, p.pyr_frame_bytes, batch,
-                                         TD_BLUR_W, DESC_WIN);
+                                         TD_BLUR_W, DESC_WIN, VS_DESC_SWIZZLE != 0);
     }
     const dim3 dgrid((p.kp_cap + 8 * VS_DESC_PER_WARP - 1) / (8 * VS_DESC_PER_WARP), batch);
     if (tma)
