@@ -255,7 +255,8 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
     __shared__ uint32_t s_hist[256];
     __shared__ VsCand s_list[LIST_CAP];
     __shared__ int s_n, s_base;
-    __shared__ uint32_t s_tx[RAW_W], s_ty[RAW_H];
+    __shared__ __align__(8) uint32_t s_tx[RAW_W];
+    __shared__ uint2 s_ty[RAW_H];       // per tile row: byte offsets of its two parent rows in the staged region, weight of the second
     __shared__ __align__(8) unsigned long long s_mbar;   // TMA completion barrier (levels >= 1)
     extern __shared__ __align__(16) uint8_t s_dyn[];   // parent region + vertical pass (levels >= 1)
 
@@ -400,8 +401,18 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             const bool isx = wid == 6;
             const uint32_t* t = tab + (isx ? L.tabx_off : L.taby_off);
             const int n = isx ? RAW_W : RAW_H, o0 = (isx ? x0 : y0) - VS_HALO, lim = isx ? W : H;
-            uint32_t* dst = isx ? s_tx : s_ty;
-            for (int c = lane; c < n; c += 32) dst[c] = __ldg(t + vs_reflect101(o0 + c, lim));
+            if (isx) {
+                for (int c = lane; c < n; c += 32) s_tx[c] = __ldg(t + vs_reflect101(o0 + c, lim));
+            } else {
+                // rows: what the vertical pass needs, ready-made -- the byte offsets of parent rows j0 and
+                // j1 = min(j0 + 1, sh - 1) inside the staged region (low / high half) and the weight of j1
+                const int sh = plan.lv[level - 1].h;
+                for (int c = lane; c < n; c += 32) {
+                    const uint32_t e = __ldg(t + vs_reflect101(o0 + c, lim));
+                    const int j0 = (int)(e & 0xffff), j1 = min(j0 + 1, sh - 1);
+                    s_ty[c] = make_uint2((uint32_t)((j0 - py0) * PW) | ((uint32_t)((j1 - py0) * PW) << 16), e >> 16);
+                }
+            }
         }
         if (PWC == 0 && !use_tma) {   // fallback (unaligned frames, very large scale factors; only in the generic instantiation): thread = one word column x every G-th row
             const int nwords = (px_hi - pxa) / 4 + 1;
@@ -458,11 +469,10 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
                 for (int k = 0; k < VIT; ++k) {
                     const int row = rg + k * G;
                     if (row < RAW_H) {
-                        const uint32_t e = s_ty[row];
-                        const int j0 = (int)(e & 0xffff);
-                        const uint32_t bq = e >> 16, wq = 256u - bq;
-                        const int j1 = min(j0 + 1, sh - 1);
-                        const uint32_t ua = par32[(j0 - py0) * PWW], ub = par32[(j1 - py0) * PWW];
+                        const uint2 e = s_ty[row];
+                        const uint32_t bq = e.y, wq = 256u - bq;
+                        const uint32_t ua = *(const uint32_t*)((const uint8_t*)par32 + (e.x & 0xffffu));
+                        const uint32_t ub = *(const uint32_t*)((const uint8_t*)par32 + (e.x >> 16));
                         const uint32_t lo = __byte_perm(ua, 0, 0x4140) * wq + __byte_perm(ub, 0, 0x4140) * bq;
                         const uint32_t hi = __byte_perm(ua, 0, 0x4342) * wq + __byte_perm(ub, 0, 0x4342) * bq;
                         dst[row * PWW] = make_uint2(lo, hi);
@@ -471,25 +481,31 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             }
         }
         __syncthreads();
-        // Horizontal: thread = one column pair x every 7th row, so that the table entries are loop invariant.
+        // Horizontal: a column pair per thread, fixed over the rows it handles, so that the table entries are loop
+        // invariant.  Lane = column pair 0 .. 31 of one row, warp w = rows w, w + 8, ...: the 32 lanes of a load read
+        // neighbouring 16-bit entries of ONE row of the vertical pass (27 words: no bank conflict; with lanes spread
+        // over two rows the second row sat 24 banks further and every load cost two wavefronts).  The four pairs
+        // 32 .. 35 of all rows follow as one pass of 152 threads.
         // A column with i0 = sw-1 has weight 0 on its right neighbour, whatever that value is.
-        const int cp = tid % (RAW_W / 2), rg7 = tid / (RAW_W / 2);       // 36 column pairs x 7 row groups
-        if (rg7 < 7) {
-            const uint32_t ea = s_tx[2 * cp], eb = s_tx[2 * cp + 1];
+        auto hpass = [&](int cp, int row0, int rstep, int nit) {
+            const uint2 et = *(const uint2*)(s_tx + 2 * cp);
+            const uint32_t ea = et.x, eb = et.y;
             const int ia = (int)(ea & 0xffff) - pxa, ib = (int)(eb & 0xffff) - pxa;
             const uint32_t aa = ea >> 16, ab = eb >> 16, wa = 256u - aa, wb = 256u - ab;
-            uint32_t* out = (uint32_t*)s_raw + rg7 * (RAW_S / 2) + cp;
-            const uint16_t* va = s_v + rg7 * PW + ia;
-            const uint16_t* vb = s_v + rg7 * PW + ib;
-#pragma unroll kResizeUnroll
-            for (int k = 0; k < (RAW_H + 6) / 7; ++k) {                    // 6 rows per thread, the last one partial
-                if (rg7 + 7 * k < RAW_H) {
-                    const uint32_t lo = (uint32_t)va[7 * k * PW] * wa + (uint32_t)va[7 * k * PW + 1] * aa + 32768u;
-                    const uint32_t hi = (uint32_t)vb[7 * k * PW] * wb + (uint32_t)vb[7 * k * PW + 1] * ab + 32768u;
-                    out[7 * k * (RAW_S / 2)] = (lo >> 16) | (hi & 0xffff0000u);
+            uint32_t* out = (uint32_t*)s_raw + row0 * (RAW_S / 2) + cp;
+            const uint16_t* va = s_v + row0 * PW + ia;
+            const uint16_t* vb = s_v + row0 * PW + ib;
+#pragma unroll
+            for (int k = 0; k < nit; ++k) {
+                if (row0 + rstep * k < RAW_H) {
+                    const uint32_t lo = (uint32_t)va[rstep * k * PW] * wa + (uint32_t)va[rstep * k * PW + 1] * aa + 32768u;
+                    const uint32_t hi = (uint32_t)vb[rstep * k * PW] * wb + (uint32_t)vb[rstep * k * PW + 1] * ab + 32768u;
+                    out[rstep * k * (RAW_S / 2)] = (lo >> 16) | (hi & 0xffff0000u);
                 }
             }
-        }
+        };
+        hpass(tid & 31, tid >> 5, 8, (RAW_H + 7) / 8);
+        if (tid < 4 * RAW_H) hpass(32 + (tid & 3), tid >> 2, 0, 1);
     }
     __syncthreads();
 
@@ -716,7 +732,7 @@ size_t vs_level_dyn_smem(const VsPlan& p)
 int vs_configure_level_smem(const VsPlan& p)
 {
     const size_t dyn = vs_level_dyn_smem(p);
-    if (dyn > 160 * 1024 || p.par_w > 1024) {
+    if (dyn > 160 * 1024 || p.par_w > 1024 || (size_t)p.par_h * p.par_w > 65535) {   // the row table holds 16-bit byte offsets into the region
         vs_set_error("scale_factor too large for the level kernel's parent staging (%zu bytes)", dyn);
         return VSLAM_E_INVALID;
     }
