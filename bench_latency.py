@@ -59,10 +59,17 @@ def run_latency(args):
     h_desc = torch.empty((1, cap, 32), dtype=torch.uint8).pin_memory()
     h_match = torch.empty((1, cap, 3), dtype=torch.int32).pin_memory()
     h_cnt = torch.empty(2, dtype=torch.int32).pin_memory()
-    s = torch.cuda.current_stream()
-    sptr = C.c_void_p(s.cuda_stream)
+    # a side stream: vslam_frontend_run replays a captured CUDA graph for small batches once it has seen an argument
+    # set (two here: the ping-pong roles of the descriptor buffers); the legacy default stream cannot be captured,
+    # so the same loop on it is the launch-by-launch comparison ("c_abi_one_frame_no_graph")
+    side = torch.cuda.Stream()
 
-    def one_frame(i, ev=None):
+    def one_frame(i, ev=None, s=side):
+        with torch.cuda.stream(s):
+            return _one_frame(i, ev, s)
+
+    def _one_frame(i, ev, s):
+        sptr = C.c_void_p(s.cuda_stream)
         cur, prv = i & 1, (i & 1) ^ 1
         d_frame[0].copy_(pin_in[i % 32], non_blocking=True)
         if ev:
@@ -89,8 +96,21 @@ def run_latency(args):
         wall.append((time.perf_counter() - t0) * 1e6)
         kern.append(ev[0].elapsed_time(ev[1]) * 1e3)
     out["c_abi_one_frame"] = dict(_pcts(wall), kernel=_pcts(kern), keypoints=int(h_cnt[0]), matches=int(h_cnt[1]),
-                                  call="H2D frame + vslam_frontend_run(batch 1, prev descriptors on device) + D2H "
-                                       "keypoints / descriptors / matches + sync")
+                                  call="H2D frame + vslam_frontend_run(batch 1, prev descriptors on device; CUDA graph "
+                                       "replay) + D2H keypoints / descriptors / matches + sync")
+    legacy = torch.cuda.default_stream()
+    torch.cuda.synchronize()
+    for i in range(20):
+        one_frame(i, None, legacy)
+    wall, kern = [], []
+    for i in range(n_calls):
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        t0 = time.perf_counter()
+        one_frame(20 + i, ev, legacy)
+        wall.append((time.perf_counter() - t0) * 1e6)
+        kern.append(ev[0].elapsed_time(ev[1]) * 1e3)
+    out["c_abi_one_frame_no_graph"] = dict(_pcts(wall), kernel=_pcts(kern), keypoints=int(h_cnt[0]), matches=int(h_cnt[1]),
+                                           call="the same on the legacy default stream: ~18 launches per call")
     orb.close()
 
     # ---- (ii) object API -------------------------------------------------------------------------------------------

@@ -363,3 +363,53 @@ def test_tracker_runs_on_the_drop_in_and_equals_the_cv2_run(synth640):
             ang = np.degrees(np.arccos(np.clip((np.trace(Ta[:3, :3] @ Tb[:3, :3].T) - 1) / 2, -1, 1)))
             assert ang < 0.5 and float(Ta[:3, 3] @ Tb[:3, 3]) > 0.99
     assert exact >= 2
+
+
+@pytest.mark.gpu
+def test_frontend_run_graph_replay_equals_plain_launches(synth640):
+    """vslam_frontend_run on small batches: the first call with an argument set runs launch by launch, the second
+    is captured into a CUDA graph, later ones replay it.  Every call must give what the plain path gives (the
+    legacy default stream is never captured: that run is the comparison)."""
+    import ctypes as C
+    import torch
+    from orbslam2 import _native
+    L = _native.lib()
+    frames = synth640.frames(0, 6)
+    h, w = frames.shape[1:]
+    orb = _native.OrbHandle(w, h, n_features=1000, max_batch=1)
+    cap = orb.kp_capacity
+    dev = torch.device("cuda", 0)
+    d_frames = torch.from_numpy(frames).to(dev)
+
+    def run(stream_ptr, sync):
+        kp = torch.zeros((1, cap, 6), dtype=torch.float32, device=dev)
+        desc = [torch.zeros((1, cap, 32), dtype=torch.uint8, device=dev) for _ in range(2)]
+        count = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(2)]
+        match = torch.zeros((1, cap, 3), dtype=torch.int32, device=dev)
+        mcount = torch.zeros(1, dtype=torch.int32, device=dev)
+        d_one = torch.empty((1, h, w), dtype=torch.uint8, device=dev)
+        outs = []
+        # every argument set (the two ping-pong buffer roles) comes round six times: plain, captured, replayed x 4
+        for rep in range(12):
+            i = rep % 6
+            cur, prv = rep & 1, (rep & 1) ^ 1
+            d_one.copy_(d_frames[i:i + 1])
+            sync()
+            _native.check(L.vslam_frontend_run(orb.handle, d_one.data_ptr(), 1, w, desc[prv].data_ptr(), count[prv].data_ptr(),
+                                               0.75, kp.data_ptr(), desc[cur].data_ptr(), count[cur].data_ptr(),
+                                               match.data_ptr(), mcount.data_ptr(), C.c_void_p(stream_ptr)))
+            sync()
+            n, m = int(count[cur][0]), int(mcount[0])
+            outs.append((n, m, kp[0, :n].cpu().numpy().copy(), desc[cur][0, :n].cpu().numpy().copy(),
+                         match[0, :m].cpu().numpy().copy()))
+        return outs
+
+    plain = run(0, torch.cuda.synchronize)                      # legacy default stream: launch by launch
+    side = torch.cuda.Stream()
+    graphed = run(side.cuda_stream, torch.cuda.synchronize)     # captured on its second sight, then replayed
+    assert len(plain) == len(graphed)
+    for a, b in zip(plain, graphed):
+        assert a[0] == b[0] and a[1] == b[1] and a[0] > 300
+        for x, y in zip(a[2:], b[2:]):
+            assert np.array_equal(x, y)
+    orb.close()

@@ -248,6 +248,11 @@ extern "C" int vslam_orb_create(const vslam_orb_params* prm, vslam_orb** out)
     ALLOC(o->d_knn_dist, B * p.kp_cap * 2 * sizeof(int32_t));
     o->knn_ws_bytes = (B + 1) * vs_knn2_tc5_workspace_per_pair(p.kp_cap);   // + 1: a batch of one matched against the previous frame expands two sets
     ALLOC(o->d_knn_ws, o->knn_ws_bytes);
+    {   // split-train kNN-2 of small batches: pairs * nsplit <= pairs + 148 * 8 / qtiles + 1 partial lists of kp_cap rows
+        const size_t qtiles = ((size_t)p.kp_cap + 255) / 256;
+        o->knn_partial_bytes = (B + 148 * 8 / qtiles + 2) * (size_t)p.kp_cap * sizeof(int4);
+        ALLOC(o->d_knn_partial, o->knn_partial_bytes);
+    }
 #undef ALLOC
     cudaError_t e = cudaMemcpy(o->d_tab, tab.data(), tab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemset(o->d_status, 0, sizeof(int32_t));
@@ -271,7 +276,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
     if (!o) return VSLAM_OK;
     cudaDeviceSynchronize();
     void* ptrs[] = {o->d_pyr, o->d_cand, o->d_stage, o->d_counters, o->d_tab, o->d_status, o->d_knn_idx,
-                    o->d_knn_dist, o->d_knn_ws, o->d_frames, o->d_bgr, o->d_track, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
+                    o->d_knn_dist, o->d_knn_ws, o->d_knn_partial, o->d_frames, o->d_bgr, o->d_track, o->d_kp, o->d_desc, o->d_count, o->d_match, o->d_match_count};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (o->stream) cudaStreamDestroy(o->stream);
     if (o->stream_in) cudaStreamDestroy(o->stream_in);
@@ -283,6 +288,7 @@ extern "C" int vslam_orb_destroy(vslam_orb* o)
         if (o->ev_done[i]) cudaEventDestroy(o->ev_done[i]);
     }
     if (o->ev_host_done) cudaEventDestroy(o->ev_host_done);
+    for (auto& g : o->graph) if (g.exec) cudaGraphExecDestroy(g.exec);
     for (cudaEvent_t e : o->prof_ev) if (e) cudaEventDestroy(e);
     delete o;
     return VSLAM_OK;

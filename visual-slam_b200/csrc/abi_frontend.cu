@@ -83,6 +83,21 @@ extern "C" int vslam_bf_match_masked_host(const uint8_t* h_query, int nq, const 
 }
 
 // ---------------------------------------------------------------------------
+static int frontend_body(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
+                         const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
+                         vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count,
+                         int32_t* d_match, int32_t* d_match_count, void* stream)
+{
+    int rc = vslam_orb_detect_and_compute(o, d_frames, batch, pitch, d_kp, d_desc, d_count, stream);
+    if (rc) return rc;
+    return vs_frontend_match(o, batch, d_prev_desc, d_prev_count, ratio, d_desc, d_count, d_match, d_match_count,
+                             (cudaStream_t)stream);
+}
+
+// batches up to this size go through a captured graph once their argument set has been seen (VSLAM_NO_GRAPH=1
+// turns it off): the per-frame call is ~18 launches of a few microseconds each
+#define VS_GRAPH_MAX_BATCH 8
+
 extern "C" int vslam_frontend_run(vslam_orb* o, const uint8_t* d_frames, int batch, int pitch,
                                   const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
                                   vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count,
@@ -90,10 +105,62 @@ extern "C" int vslam_frontend_run(vslam_orb* o, const uint8_t* d_frames, int bat
 {
     VS_REQUIRE(o && d_match && d_match_count, "null argument");
     VS_REQUIRE(!d_prev_desc || d_prev_count, "d_prev_count required with d_prev_desc");
-    int rc = vslam_orb_detect_and_compute(o, d_frames, batch, pitch, d_kp, d_desc, d_count, stream);
-    if (rc) return rc;
-    return vs_frontend_match(o, batch, d_prev_desc, d_prev_count, ratio, d_desc, d_count, d_match, d_match_count,
-                             (cudaStream_t)stream);
+    static const int no_graph = getenv("VSLAM_NO_GRAPH") && atoi(getenv("VSLAM_NO_GRAPH")) != 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    // the legacy default stream cannot be captured; profiling records events between the launches
+    const bool graphable = batch >= 1 && batch <= VS_GRAPH_MAX_BATCH && !no_graph && !o->graph_off && !o->prof_on &&
+                           s != nullptr && s != cudaStreamLegacy && !o->knn_no_split;
+    if (!graphable)
+        return frontend_body(o, d_frames, batch, pitch, d_prev_desc, d_prev_count, ratio, d_kp, d_desc, d_count, d_match,
+                             d_match_count, stream);
+    uint64_t key[12] = {(uint64_t)(uintptr_t)d_frames, (uint64_t)batch, (uint64_t)pitch, (uint64_t)(uintptr_t)d_prev_desc,
+                        (uint64_t)(uintptr_t)d_prev_count, 0, (uint64_t)(uintptr_t)d_kp, (uint64_t)(uintptr_t)d_desc,
+                        (uint64_t)(uintptr_t)d_count, (uint64_t)(uintptr_t)d_match, (uint64_t)(uintptr_t)d_match_count,
+                        ((uint64_t)o->dist_mode << 32) | (uint32_t)o->ini_threshold};
+    memcpy(&key[5], &ratio, sizeof(double));
+    vslam_orb::GraphSlot* slot = nullptr;
+    for (auto& g : o->graph)
+        if (g.seen && !memcmp(g.key, key, sizeof(key))) { slot = &g; break; }
+    if (slot && slot->exec) {
+        VS_CUDA(cudaGraphLaunch(slot->exec, s));
+        o->last_stream = s;
+        o->last_frames = d_frames; o->last_pitch = pitch; o->last_batch = batch;
+        return VSLAM_OK;
+    }
+    if (!slot) {
+        // first sight of this argument set: run it launch by launch (this also leaves every lazily configured kernel
+        // attribute and scratch buffer in place) and remember it
+        slot = &o->graph[o->graph_next];
+        o->graph_next = (o->graph_next + 1) % (int)(sizeof(o->graph) / sizeof(o->graph[0]));
+        if (slot->exec) { cudaGraphExecDestroy(slot->exec); slot->exec = nullptr; }
+        memcpy(slot->key, key, sizeof(key));
+        slot->seen = 1;
+        return frontend_body(o, d_frames, batch, pitch, d_prev_desc, d_prev_count, ratio, d_kp, d_desc, d_count, d_match,
+                             d_match_count, stream);
+    }
+    // second sight: capture the same launches, instantiate, replay from now on
+    if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        o->graph_off = 1;
+        return frontend_body(o, d_frames, batch, pitch, d_prev_desc, d_prev_count, ratio, d_kp, d_desc, d_count, d_match,
+                             d_match_count, stream);
+    }
+    const int rc = frontend_body(o, d_frames, batch, pitch, d_prev_desc, d_prev_count, ratio, d_kp, d_desc, d_count, d_match,
+                                 d_match_count, stream);
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(s, &graph);
+    if (rc == VSLAM_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&slot->exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (rc != VSLAM_OK || e != cudaSuccess || !slot->exec) {
+        // capture is not available here (or the body failed): nothing was executed, so run it plainly and stop trying
+        cudaGetLastError();
+        slot->exec = nullptr;
+        o->graph_off = 1;
+        return frontend_body(o, d_frames, batch, pitch, d_prev_desc, d_prev_count, ratio, d_kp, d_desc, d_count, d_match,
+                             d_match_count, stream);
+    }
+    VS_CUDA(cudaGraphLaunch(slot->exec, s));
+    return VSLAM_OK;
 }
 
 // matching half of the front end: pair 0 = (previous boundary frame, frame 0) when given, then

@@ -176,7 +176,10 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     }
     std::unique_lock<std::mutex> lock(g_partial_mu, std::defer_lock);
     KnnScratch* sc = nullptr;
-    if (nsplit > 1) {
+    // a handle brings its own partial lists (no process-wide scratch, no cross-stream events: capturable)
+    const bool own_partial = nsplit > 1 && prof && prof->d_knn_partial &&
+                             (size_t)pairs * nsplit * nq * sizeof(int4) <= prof->knn_partial_bytes;
+    if (nsplit > 1 && !own_partial) {
         int dev = 0;
         VS_CUDA(cudaGetDevice(&dev));
         VS_REQUIRE(dev >= 0 && dev < VS_MAX_DEVICES, "device ordinal out of range");
@@ -191,7 +194,7 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
         // another stream may still be reading / writing the scratch: order this launch behind it
         if (sc->ev && sc->last != s) VS_CUDA(cudaStreamWaitEvent(s, sc->ev, 0));
     }
-    int4* partial = sc ? sc->partial : nullptr;
+    int4* partial = own_partial ? prof->d_knn_partial : sc ? sc->partial : nullptr;
     vs_prof_mark(prof, VS_PROF_KNN2, s);
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
     if (tc5) {
@@ -205,9 +208,11 @@ int vs_launch_knn2(vslam_orb* prof, const uint8_t* d_q, int nq, long q_stride, c
     if (nsplit > 1) {
         __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
         vs_knn2_merge_kernel<<<dim3((nq + 255) / 256, pairs), 256, 0, s>>>(partial, nq, d_nq, nsplit, d_idx, d_dist);
-        if (!sc->ev) VS_CUDA(cudaEventCreateWithFlags(&sc->ev, cudaEventDisableTiming));
-        VS_CUDA(cudaEventRecord(sc->ev, s));
-        sc->last = s;
+        if (sc) {
+            if (!sc->ev) VS_CUDA(cudaEventCreateWithFlags(&sc->ev, cudaEventDisableTiming));
+            VS_CUDA(cudaEventRecord(sc->ev, s));
+            sc->last = s;
+        }
     }
     VS_CUDA(cudaGetLastError());
     return VSLAM_OK;

@@ -95,6 +95,8 @@ struct vslam_orb {
     int32_t* d_knn_dist;
     uint8_t* d_knn_ws;     // expanded descriptor tiles of the tcgen05 kNN-2: [max_batch + 1] x vs_knn2_tc5_workspace_per_pair(kp_cap)
     size_t knn_ws_bytes;   // bytes available from d_knn_ws (a chunk view of the handle sees its own slice)
+    int4* d_knn_partial;   // partial top-2 lists of the split-train kNN-2 (small batches), owned by the handle so that
+    size_t knn_partial_bytes;   // such a call needs neither the process-wide scratch nor its events (graph capture)
     // host staging for *_host entry points
     uint8_t* d_frames;     // [max_batch][h][pitch0]
     uint8_t* d_track;      // outputs + workspace of vslam_track_clip_host (lazy, one block)
@@ -113,6 +115,15 @@ struct vslam_orb {
     cudaEvent_t ev_in[VS_HOST_CHUNKS], ev_ext[VS_HOST_CHUNKS], ev_done[VS_HOST_CHUNKS];
     cudaEvent_t ev_host_done;  // blocking-sync event: end of a *_host call (the waiting host thread sleeps instead of spinning)
     int knn_no_split;          // set on the per-chunk views: the split-train scratch of kNN-2 is not per stream
+    // CUDA graphs of vslam_frontend_run for small batches (the per-frame call of the reference's Tracker): a call is
+    // a chain of ~18 short launches, and at batch 1 the launch gaps are as long as the kernels.  A call whose
+    // arguments were seen before is captured once and replayed (VS_GRAPH_SLOTS argument sets, round robin).
+    struct GraphSlot {
+        uint64_t key[12];
+        int seen;
+        cudaGraphExec_t exec;
+    } graph[4];
+    int graph_next, graph_off;
     cudaStream_t last_stream;
     const uint8_t* last_frames;  // level-0 pixels of the last batch (for debug taps)
     int last_pitch, last_batch;
