@@ -130,6 +130,11 @@ __device__ __forceinline__ int fast_single(const uint16_t* p, int thr)
     return s > 0 ? s : 0;
 }
 
+__device__ __forceinline__ void sts_u16(uint32_t saddr, uint32_t v)
+{
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(saddr), "h"((uint16_t)v) : "memory");
+}
+
 __device__ __forceinline__ uint32_t fsr16(uint32_t lo, uint32_t hi) { return __funnelshift_r(lo, hi, 16); }
 
 // u16 lane -> float: I2F.U16 takes either half of a register directly (XU pipe, which is otherwise
@@ -566,12 +571,16 @@ vs_level_kernel(const __grid_constant__ VsPlan plan, int level, const uint8_t* _
             basepos = __shfl_sync(0xffffffffu, basepos, 0);
             const uint32_t lt = (1u << lane) - 1u;
             const int r0 = tid >> 4;
-            const int p01 = basepos + __popc(mk[0] & lt) + __popc(mk[1] & lt);
-            const int p23 = basepos + c01 + __popc(mk[2] & lt) + __popc(mk[3] & lt);
-            if (need[0]) s_queue[p01] = (uint16_t)((r0 << 6) | (2 * w + 2));
-            if (need[1]) s_queue[p01 + (need[0] != 0)] = (uint16_t)((r0 << 6) | (2 * w + 3));
-            if (need[2]) s_queue[p23] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 2));
-            if (need[3]) s_queue[p23 + (need[2] != 0)] = (uint16_t)(((r0 + 16) << 6) | (2 * w + 3));
+            // shared-window addresses and entry values once, then four predicated 16-bit stores (written as indexed
+            // array stores the compiler rebuilt base, index and value for each of them: ~40 instructions)
+            const uint32_t q_u = (uint32_t)__cvta_generic_to_shared(s_queue);
+            const uint32_t a01 = q_u + 2u * (uint32_t)(basepos + __popc(mk[0] & lt) + __popc(mk[1] & lt));
+            const uint32_t a23 = q_u + 2u * (uint32_t)(basepos + c01 + __popc(mk[2] & lt) + __popc(mk[3] & lt));
+            const uint32_t e0 = (uint32_t)((r0 << 6) | (2 * w + 2));
+            if (need[0]) sts_u16(a01, e0);
+            if (need[1]) sts_u16(a01 + (need[0] ? 2u : 0u), e0 + 1u);
+            if (need[2]) sts_u16(a23, e0 + (16u << 6));
+            if (need[3]) sts_u16(a23 + (need[2] ? 2u : 0u), e0 + (16u << 6) + 1u);
         }
     }
     if (tid >= 256 - 2 * SC_H) {   // ring columns tx = -1 (word 1, high lane) and tx = TW (word TW/2 + 2, low lane)
