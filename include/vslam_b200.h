@@ -275,7 +275,12 @@ int vslam_bf_match_masked_host(const uint8_t* h_query, int nq, const uint8_t* h_
  * If d_prev_desc is non-NULL it is the descriptor block (kp_capacity rows, count
  * *d_prev_count) of the frame preceding frame 0 (the previous batch's or the
  * neighbouring rank's boundary frame); the outputs then hold `batch` pairs and
- * pair 0 is (prev, frame 0). */
+ * pair 0 is (prev, frame 0).
+ * Small batches (<= 8 frames: the per-frame call of Tracker.process_frame,
+ * tracker.py:87,214) on a stream other than the legacy default stream are captured
+ * into a CUDA graph the second time an argument set is seen and replayed afterwards
+ * (four argument sets per handle, e.g. ping-pong descriptor buffers); results are
+ * those of the plain launches.  VSLAM_NO_GRAPH=1 turns this off. */
 int vslam_frontend_run(vslam_orb* orb, const uint8_t* d_frames, int batch, int pitch,
                        const uint8_t* d_prev_desc, const int32_t* d_prev_count, double ratio,
                        vslam_keypoint* d_kp, uint8_t* d_desc, int32_t* d_count,
