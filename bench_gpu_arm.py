@@ -408,17 +408,25 @@ def run_gpu_arm(args, rank, world, B):
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         # measured DRAM traffic of the level launches of one step (ncu --set full capture committed under
         # profiles/); only quoted when it was taken on this workload and batch
-        traffic, traffic_src = None, None
+        traffic, traffic_src, level_winst = None, None, None
         for name in ("r2_level_traffic.json", "r1_level_traffic.json"):
             try:
                 tj = json.load(open(os.path.join(BN.ROOT, "profiles", name)))
                 if tj.get("workload") == args.workload and int(tj.get("frames_per_step", 0)) == B:
                     traffic = int(tj["dram_read_bytes"]) + int(tj["dram_write_bytes"])
                     traffic_src = tj.get("source")
+                    level_winst = tj.get("warp_instructions")
                     break
             except Exception:
                 pass
         level_ms = float(prof[:16].sum())
+        issue_slots = None
+        if level_winst and level_ms > 0:
+            sm_hz = float((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+            sms = torch.cuda.get_device_properties(0).multi_processor_count
+            ach = level_winst / (level_ms / K * 1e-3)
+            issue_slots = {"warp_instructions_per_step": int(level_winst), "achieved_ginst_s": ach / 1e9,
+                           "peak_ginst_s": sms * 4 * sm_hz / 1e9, "frac": ach / (sms * 4 * sm_hz)}
         lvl_bytes = BN.level_kernel_bytes(w, h) * B * K
         achieved = lvl_bytes / (level_ms * 1e-3) / 1e9 if level_ms > 0 else 0.0
         breakdown = {("level%d" % i): round(float(prof[i]) / K, 4) for i in range(BN.N_LEVELS)}
@@ -450,7 +458,11 @@ def run_gpu_arm(args, rank, world, B):
                          "algorithmic_bytes_per_frame": BN.level_kernel_bytes(w, h),
                          "algorithmic_bytes_per_step": BN.level_kernel_bytes(w, h) * B, "traffic": traffic,
                          "traffic_note": traffic_src,
-                         "ms_per_step": level_ms / K},
+                         "ms_per_step": level_ms / K,
+                         # what actually bounds it: the warp-instruction issue slots (4 schedulers per SM, one warp
+                         # instruction per clock each).  Instruction count of the 8 launches from the same ncu capture as
+                         # `traffic`; rate over the live-timed duration at the SM clock sampled during the timed region
+                         "issue_slots": issue_slots},
             "extraction": {"ms_per_step": float(prof[:19].sum()) / K,
                            "algorithmic_bytes_per_frame": BN.extraction_bytes(w, h, nf),
                            "achieved_gbs": BN.extraction_bytes(w, h, nf) * B * K / (prof[:19].sum() * 1e-3) / 1e9

@@ -38,7 +38,8 @@ def main():
     hdr, units, body = rows[0], rows[1], rows[2:]
     col = {n: i for i, n in enumerate(hdr)}
     kname = col["Kernel Name"]
-    out, level_rd, level_wr, n_level = [], 0.0, 0.0, 0
+    out, level_rd, level_wr, level_inst, n_level = [], 0.0, 0.0, 0.0, 0
+    i_inst = [c[0] for c in COLS].index("warp_inst")
     for r in body:
         name = r[kname]
         short = name.split("(")[0].replace("void ", "")
@@ -58,6 +59,7 @@ def main():
             if n_level <= 8:
                 level_rd += vals[1] * 1e6
                 level_wr += vals[2] * 1e6
+                level_inst += float(vals[i_inst] or 0)
         out.append([short] + [("%.4g" % v if isinstance(v, float) else v) for v in vals])
     with open(out_csv, "w") as f:
         f.write("# ncu --set full --clock-control none, bench.py --steps 2 --warmup 1 --no-cpu (C2, 512 frames/step)\n")
@@ -68,6 +70,7 @@ def main():
     if out_json and n_level >= 8:
         json.dump({"workload": "c2", "frames_per_step": 512, "kernel": "vs_level_kernel", "launches": 8,
                    "dram_read_bytes": int(level_rd), "dram_write_bytes": int(level_wr),
+                   "warp_instructions": int(level_inst),
                    "source": "%s (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum summed over the 8 "
                              "level launches of one step)" % out_csv}, open(out_json, "w"), indent=1)
     print("wrote", out_csv, len(out), "launches")
