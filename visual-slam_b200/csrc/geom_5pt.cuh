@@ -34,9 +34,11 @@ VS_HD inline double poly_eval(const double* q, int n, double x)
 
 // The single root of q (degree n) in a bracket [xl, xh] over which q is monotone and changes sign; `up`: q
 // increases through the root.  Newton from the midpoint, bisection whenever a step leaves the bracket.
-VS_HD inline double poly_root_in(const double* q, int n, double xl, double xh, bool up, double tol)
+// fl, fh: q at the bracket ends (known to every caller): the first iterate is the secant point, not the midpoint.
+VS_HD inline double poly_root_in(const double* q, int n, double xl, double xh, bool up, double tol, double fl, double fh)
 {
-    double x = 0.5 * (xl + xh);
+    double x = (xl * fh - xh * fl) / (fh - fl);
+    if (!(x > xl && x < xh)) x = 0.5 * (xl + xh);
     for (int it = 0; it < 80; ++it) {
         double f = q[n], fp = 0.0;
         for (int i = n - 1; i >= 0; --i) { fp = fp * x + f; f = f * x + q[i]; }
@@ -102,10 +104,11 @@ VS_HD inline int real_roots_deg10(const double* c, double* roots, bool* deflated
             const bool neg_inf_negative = (n & 1) != 0;
             if (fprev != 0.0 && ((fprev < 0.0) != neg_inf_negative)) {
                 double h = 0.25 * (1.0 + fabs(a0)), xin = a0;
+                double fin = fprev;
                 for (int it = 0; it < 64; ++it, h *= 2.0) {
-                    const double xo = a0 - h;
-                    if ((poly_eval(q, n, xo) < 0.0) == neg_inf_negative) { next[nr++] = poly_root_in(q, n, xo, xin, neg_inf_negative, tol); break; }
-                    xin = xo;
+                    const double xo = a0 - h, fo = poly_eval(q, n, xo);
+                    if ((fo < 0.0) == neg_inf_negative) { next[nr++] = poly_root_in(q, n, xo, xin, neg_inf_negative, tol, fo, fin); break; }
+                    xin = xo; fin = fo;
                     if (h > 2.0 * B) break;
                 }
             } else if (fprev == 0.0 && nc == 0) {
@@ -119,7 +122,7 @@ VS_HD inline int real_roots_deg10(const double* c, double* roots, bool* deflated
             if (iv + 1 == nc) break;
             const double fhi = poly_eval(q, n, hi);
             if (hi > lo && fprev != 0.0 && fhi != 0.0 && ((fprev < 0.0) != (fhi < 0.0)))
-                next[nr++] = poly_root_in(q, n, lo, hi, fprev < 0.0, tol);
+                next[nr++] = poly_root_in(q, n, lo, hi, fprev < 0.0, tol, fprev, fhi);
             fprev = fhi;
         }
         // (last anchor, +inf): q(+inf) > 0
@@ -127,10 +130,11 @@ VS_HD inline int real_roots_deg10(const double* c, double* roots, bool* deflated
             const double a1 = nc > 0 ? crit[nc - 1] : 0.0;
             if (fprev < 0.0) {
                 double h = 0.25 * (1.0 + fabs(a1)), xin = a1;
+                double fin = fprev;
                 for (int it = 0; it < 64; ++it, h *= 2.0) {
-                    const double xo = a1 + h;
-                    if (poly_eval(q, n, xo) > 0.0) { next[nr++] = poly_root_in(q, n, xin, xo, true, tol); break; }
-                    xin = xo;
+                    const double xo = a1 + h, fo = poly_eval(q, n, xo);
+                    if (fo > 0.0) { next[nr++] = poly_root_in(q, n, xin, xo, true, tol, fin, fo); break; }
+                    xin = xo; fin = fo;
                     if (h > 2.0 * B) break;
                 }
             }
