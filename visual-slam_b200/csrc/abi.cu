@@ -347,7 +347,7 @@ extern "C" int vslam_orb_detect_and_compute(vslam_orb* o, const uint8_t* d_frame
     o->last_frames = d_frames;
     o->last_pitch = pitch;
     o->last_batch = batch;
-    o->prof_count = 0;
+    if (o->prof_on != 2) o->prof_count = 0;      // 2: marks accumulate over calls until they are read
     int rc = vs_launch_levels(o, d_frames, batch, pitch, s);
     if (rc) return rc;
     return vs_launch_select(o, d_frames, batch, pitch, d_kp, d_desc, d_count, s);
@@ -453,7 +453,7 @@ extern "C" int vslam_orb_debug_run_levels_host(vslam_orb* o, const uint8_t* h_fr
 extern "C" int vslam_orb_set_profiling(vslam_orb* o, int enable)
 {
     VS_REQUIRE(o, "null handle");
-    o->prof_on = enable ? 1 : 0;
+    o->prof_on = enable == 2 ? 2 : enable ? 1 : 0;
     o->prof_count = 0;
     return VSLAM_OK;
 }
@@ -470,5 +470,6 @@ extern "C" int vslam_orb_read_profile(vslam_orb* o, float* h_ms, int n_slots)
         VS_CUDA(cudaEventElapsedTime(&ms, o->prof_ev[i], o->prof_ev[i + 1]));
         h_ms[o->prof_slot[i]] += ms;
     }
+    if (o->prof_on == 2) o->prof_count = 0;
     return VSLAM_OK;
 }

@@ -143,7 +143,7 @@ extern "C" int vslam_orb_compute(vslam_orb* o, const uint8_t* d_frame, int pitch
     const VsPlan& p = o->plan;
     cudaStream_t s = (cudaStream_t)stream;
     o->last_stream = s; o->last_frames = d_frame; o->last_pitch = pitch; o->last_batch = 1;
-    o->prof_count = 0;
+    if (o->prof_on != 2) o->prof_count = 0;
     int rc = vs_launch_levels(o, d_frame, 1, pitch, s);           // pyramid + blurred levels of this frame
     if (rc) return rc;
     __atomic_fetch_add(&g_vs_launches, 1ull, __ATOMIC_RELAXED);
@@ -188,7 +188,7 @@ extern "C" int vslam_orb_compute_host(vslam_orb* o, const uint8_t* h_frame, cons
     cudaStream_t s = o->stream;
     VS_CUDA(cudaMemcpyAsync(o->d_frames, h_frame, (size_t)p.width * p.height, cudaMemcpyHostToDevice, s));
     o->last_stream = s; o->last_frames = o->d_frames; o->last_pitch = p.width; o->last_batch = 1;
-    o->prof_count = 0;
+    if (o->prof_on != 2) o->prof_count = 0;
     rc = vs_launch_levels(o, o->d_frames, 1, p.width, s);
     if (rc) return rc;
     VsGivenKp* d_k = nullptr;
