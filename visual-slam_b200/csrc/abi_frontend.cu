@@ -212,8 +212,10 @@ extern "C" int vslam_frontend_run_host(vslam_orb* o, const uint8_t* h_frames, in
     // the head of the next.  A chunk after the first is matched against the last frame of its
     // predecessor (its descriptors are ready at ev_ext[k-1]), so the match rows come out exactly as
     // for one undivided batch.  Host buffers should be pinned.
+    static const int max_chunks = getenv("VSLAM_HOST_CHUNKS") ? atoi(getenv("VSLAM_HOST_CHUNKS")) : VS_HOST_CHUNKS;
     int nchunks = batch / 16;
     nchunks = nchunks < 1 ? 1 : nchunks > VS_HOST_CHUNKS ? VS_HOST_CHUNKS : nchunks;
+    if (max_chunks >= 1 && nchunks > max_chunks) nchunks = max_chunks;
     const int chunk = (batch + nchunks - 1) / nchunks;
     const int saved_prof = o->prof_on;
     o->prof_on = 0;   // the per-kernel marks describe one undivided run
