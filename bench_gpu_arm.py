@@ -215,7 +215,7 @@ def run_gpu_arm(args, rank, world, B):
     # per-kernel events are recorded between the launches of the timed steps themselves; they accumulate on the
     # handle (mode 2) and are read once behind the timed region, so that the steps queue back to back like a
     # caller's would (a read per step is a host synchronisation per step: ~0.08 ms of idle GPU at C2)
-    accumulate = K * 24 <= 1000
+    accumulate = K * 24 <= 8000
     L.vslam_orb_set_profiling(orb.handle, 2 if accumulate else 1)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

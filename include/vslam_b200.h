@@ -207,7 +207,7 @@ int vslam_gftt_grid(const uint8_t* d_frame, int height, int width, int rows, int
  * vslam_orb_read_profile waits for the last call and returns its milliseconds per slot:
  * [0..15] fused level kernel per pyramid level, [16] Harris, [17] select, [18] describe,
  * [19] kNN-2 (+ merge), [20] ratio filter; n_slots must be >= 24.
- * enable = 2: the marks of successive calls accumulate (up to 1024 marks, ~45 front-end
+ * enable = 2: the marks of successive calls accumulate (up to 8192 marks, ~340 front-end
  * calls) and vslam_orb_read_profile returns the sums since the last read -- a timed loop
  * then needs no host synchronisation per call. */
 int vslam_orb_set_profiling(vslam_orb* orb, int enable);

@@ -75,7 +75,7 @@ struct VsPlan {
 #define VS_PROF_KNN2 19
 #define VS_PROF_RATIO 20
 #define VS_PROF_SLOTS 24
-#define VS_PROF_MAX_MARKS 1024     // marks of one call (enable = 1) or of the calls since the last read (enable = 2)
+#define VS_PROF_MAX_MARKS 8192     // marks of one call (enable = 1) or of the calls since the last read (enable = 2)
 
 #define VS_HOST_CHUNKS 8
 
